@@ -1,0 +1,280 @@
+#!/usr/bin/env python
+"""Headline benchmark: TinyECG FedAvg, ECG samples/s per FL round (+ exposed aggregation ms/round).
+
+Config (the reference's sweep config, ``TRUE_FL_M3/run_part3_sweep.sh:38-49``, on synthetic data):
+TinyECG(num_classes=2), windows 1x500, batch 256 per client, 50 local SGD(1e-2, 0.9) steps per round,
+config G1 (AMP), one client per GPU, FedAvg aggregation every round.  One bench "step" = one FL round
+(50 local steps + aggregation).  ``value`` = whole-job samples/s = N * K * 50 * 256 / t, where t is the
+device time (CUDA events, max over ranks) of K rounds INCLUDING aggregation.
+
+    python bench.py --gpus 1 --steps 20 --warmup 3
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
+        --master-port P bench.py --gpus N --steps K --warmup W
+    python bench.py --impl reference ...      # the unmodified reference under baseline/_ref
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import tempfile
+import time
+
+REPO = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, REPO)
+
+METRIC = "ECG samples/sec per FL round (TinyECG FedAvg, aggregation included)"
+BATCH, LOCAL_STEPS, WIN_LEN, NUM_CLASSES = 256, 50, 500, 2
+# 131072 windows x 500 x 4 B = 262 MB per client: larger than the 126 MB L2, so the random-batch
+# gather of every round comes from HBM (timing rule: inputs larger than L2).
+NUM_WINDOWS = 131072
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20, help="timed FL rounds")
+    ap.add_argument("--warmup", type=int, default=3, help="untimed FL rounds")
+    ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
+    ap.add_argument("--amp", choices=["bf16", "fp16", "none"], default="bf16")
+    ap.add_argument("--agg-backend", default="auto")
+    ap.add_argument("--num-windows", type=int, default=NUM_WINDOWS)
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def make_shards(root: str, rank: int, n: int) -> str:
+    """Synthetic Gaussian windows of the reference's shape, one shard directory per client."""
+    import numpy as np
+    from crossscale.data.shard_format import shard_name, write_shard
+    d = os.path.join(root, f"client_{rank}")
+    rng = np.random.default_rng(1337 + rank)
+    per = 32768
+    for i, lo in enumerate(range(0, n, per)):
+        m = min(per, n - lo)
+        write_shard(os.path.join(d, shard_name(i)), rng.standard_normal((m, WIN_LEN), dtype=np.float32))
+    return d
+
+
+def emit(obj):
+    print(json.dumps(obj), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from crossscale.data.shard_dataset import load_shards_to_gpu
+    from crossscale.data.staging import PinnedShardStore
+    from crossscale.fl.engine import FedAvgRunner
+    from crossscale.models import TinyECG
+    from crossscale.parallel import launch
+    from crossscale.utils.clocks import ClockSampler
+    from crossscale.utils.misc import set_basic_seeds, setup_device
+    from crossscale.utils.timing import max_over_ranks
+    from glob import glob
+
+    rank, world, local_rank = launch.init_distributed()
+    if not torch.cuda.is_available():
+        emit({"metric": METRIC, "error": "no CUDA device", "n_gpus": 0})
+        return
+    device = setup_device(local_rank)
+    set_basic_seeds(1234 + rank)
+    K, W = args.steps, max(args.warmup, 3)
+    tmp = tempfile.mkdtemp(prefix="cs_bench_")
+    shard_dir = make_shards(tmp, rank, args.num_windows)
+    paths = sorted(glob(os.path.join(shard_dir, "ecg_*.bin")))
+    x_gpu, y_gpu = load_shards_to_gpu(paths, device=device, max_windows=args.num_windows)
+
+    model = TinyECG(num_classes=NUM_CLASSES).to(device)
+    cfg = "G0" if args.amp == "none" else "G1"
+    runner = FedAvgRunner(model, device, x_gpu, y_gpu, BATCH, LOCAL_STEPS, cfg, amp=args.amp, rank=rank,
+                          world=world, agg_backend=args.agg_backend)
+
+    def sync_all():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-timed rounds (GPU-resident data, like the reference) ----------------------------
+    for _ in range(W):
+        runner.run_round_async()
+    sync_all()
+    launches0 = runner.trainer.launches + runner.agg.launches
+    sampler = ClockSampler(gpu_index=torch.cuda.current_device()).start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(K):
+        runner.run_round_async()
+    e1.record()
+    sync_all()
+    dev_ms = max_over_ranks(e0.elapsed_time(e1), device)
+    launches = runner.trainer.launches + runner.agg.launches - launches0
+    # aggregation alone (exposed: nothing overlaps it), device-timed
+    a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sync_all()
+    a0.record()
+    for _ in range(K):
+        runner.agg.aggregate(runner.flat, runner.prev, runner.weight, runner.mom)
+    a1.record()
+    sync_all()
+    agg_ms = max_over_ranks(a0.elapsed_time(a1), device) / K
+    loss_dev = runner.trainer.state.loss_sum()
+
+    samples = world * K * LOCAL_STEPS * BATCH
+    value = samples / (dev_ms / 1e3)
+
+    # ---- end-to-end rounds: pinned host -> H2D every round, loss D2H every round -------------------
+    e2e = None
+    if not args.no_e2e:
+        dt = torch.bfloat16 if args.amp == "bf16" else torch.float32
+        store = PinnedShardStore(paths, max_windows=args.num_windows, dtype=dt)
+        runner.enable_e2e(store, seed=rank)
+        for _ in range(W):
+            runner.run_round_e2e()
+        sync_all()
+        t0 = time.perf_counter()
+        e0.record()
+        last = 0.0
+        for _ in range(K):
+            last = runner.run_round_e2e()
+        e1.record()
+        sync_all()
+        wall_ms = (time.perf_counter() - t0) * 1e3
+        e2e_ms = max_over_ranks(max(e0.elapsed_time(e1), wall_ms), device)
+        e2e = {"value": samples / (e2e_ms / 1e3), "unit": "samples/s",
+               "h2d_bytes_per_step": int(runner._stager.h2d_bytes), "d2h_bytes_per_step": int(runner.d2h_bytes),
+               "ms_per_step": e2e_ms / K, "stage_dtype": str(dt).replace("torch.", ""), "last_loss": last}
+    clocks = sampler.stop()
+    status = runner.agg.comm.status() if getattr(runner.agg, "comm", None) is not None else 0
+
+    if rank == 0:
+        base = None
+        try:
+            with open(os.path.join(REPO, "BASELINE.json")) as f:
+                pub = json.load(f).get("published", {})
+            base = pub.get("samples_per_s") if isinstance(pub, dict) else None
+        except Exception:
+            pass
+        out = {
+            "metric": METRIC, "value": value, "unit": "samples/s", "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": dev_ms / K, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": (value / base) if base else None,
+            "dtype": {"bf16": "bf16", "fp16": "fp16", "none": "fp32"}[args.amp], "data": "synthetic",
+            "impl": "ours",
+            "config": {"model": "TinyECG(num_classes=2)", "global_batch": BATCH * world, "seq_len": WIN_LEN,
+                       "parallelism": f"fedavg{world} (1 client/GPU)", "local_steps": LOCAL_STEPS,
+                       "batch_per_client": BATCH, "fl_config": cfg, "step": "one FL round = 50 local steps + aggregation",
+                       "windows_per_client": args.num_windows,
+                       "l2": "inputs larger than L2 (262 MB resident dataset per client, random gather)",
+                       "aggregation": runner.agg.backend},
+            "exposed_agg_ms_per_round": agg_ms, "avg_loss": loss_dev / max(1, (W + K) * LOCAL_STEPS),
+            "clocks": clocks, "gpu_launches": int(launches), "comm_status": status,
+        }
+        if e2e is not None:
+            out["e2e"] = e2e
+        emit(out)
+    runner.close()
+    launch.shutdown()
+
+
+# ------------------------------------------------------------------------------------------------
+def run_reference(args):
+    ref_root = os.path.join(REPO, "baseline", "_ref")
+    script_dir = os.path.join(ref_root, "Module_3", "TRUE_FL_M3")
+    script = os.path.join(script_dir, "part3_fedavg_overlap_mpi_gpu.py")
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if not os.path.exists(script):
+        if rank == 0:
+            emit({"impl": "reference", "unavailable": "baseline/_ref missing (run python baseline/install_reference.py; "
+                  "pip cannot install the reference: no setup.py/pyproject.toml)"})
+        return
+    # the reference puts every rank on cuda:0 -> give each rank its own device
+    os.environ["CUDA_VISIBLE_DEVICES"] = os.environ.get("LOCAL_RANK", "0")
+    import runpy
+    import warnings
+    import torch
+    if not torch.cuda.is_available():
+        if rank == 0:
+            emit({"impl": "reference", "unavailable": "no CUDA device"})
+        return
+    sys.path.insert(0, os.path.join(REPO, "baseline", "mpi_shim"))   # mpi4py is not in the image
+    sys.path.insert(0, script_dir)
+    K, W = args.steps, max(args.warmup, 3)
+    # one directory for the whole job: every rank is a child of the same torchrun agent
+    tmp = (tempfile.mkdtemp(prefix="cs_bench_ref_") if world == 1
+           else os.path.join(tempfile.gettempdir(), f"cs_bench_ref_{os.getppid()}"))
+    os.makedirs(tmp, exist_ok=True)
+    # all ranks see one shard directory; the reference stripes shards over ranks itself
+    import numpy as np
+    from crossscale.data.shard_format import shard_name, write_shard
+    shard_dir = os.path.join(tmp, "shards")
+    if rank == 0:
+        per = args.num_windows
+        for r in range(world):
+            rng = np.random.default_rng(1337 + r)
+            write_shard(os.path.join(shard_dir, shard_name(r)), rng.standard_normal((per, WIN_LEN), dtype=np.float32))
+        open(os.path.join(tmp, "ready"), "w").close()
+    else:
+        while not os.path.exists(os.path.join(tmp, "ready")):
+            time.sleep(0.05)
+    csv = os.path.join(ref_root, "Module_3", "results", "fedavg_results.csv")
+    if rank == 0 and os.path.exists(csv):
+        os.remove(csv)
+    from crossscale.utils.clocks import ClockSampler
+    sampler = ClockSampler(gpu_index=int(os.environ.get("LOCAL_RANK", "0"))).start()
+    argv = [script, "--data-root", shard_dir, "--batch-size", str(BATCH), "--rounds", str(W + K),
+            "--local-steps", str(LOCAL_STEPS), "--max-windows", str(args.num_windows), "--config", "G1"]
+    old = sys.argv
+    sys.argv = argv
+    try:
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            runpy.run_path(script, run_name="__main__")
+    finally:
+        sys.argv = old
+    clocks = sampler.stop()
+    if rank != 0:
+        return
+    import csv as _csv
+    with open(csv) as f:
+        rows = [r for r in _csv.DictReader(f) if r["config"] == "G1" and int(r["round_idx"]) >= W]
+    per_rank = {}
+    for r in rows:
+        per_rank.setdefault(int(r["rank"]), []).append(float(r["local_train_ms"]) + float(r["comm_ms"]))
+    total_ms = max(sum(v) for v in per_rank.values())
+    comm_ms = max(float(r["comm_ms"]) for r in rows)
+    samples = world * K * LOCAL_STEPS * BATCH
+    value = samples / (total_ms / 1e3)
+    emit({"metric": METRIC, "value": value, "unit": "samples/s", "n_gpus": world, "steps": K, "warmup": W,
+          "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+          "dtype": "fp16", "data": "synthetic", "impl": "reference",
+          "config": {"model": "TinyECG(num_classes=2)", "global_batch": BATCH * world, "seq_len": WIN_LEN,
+                     "parallelism": f"fedavg{world} (1 client/GPU)", "local_steps": LOCAL_STEPS,
+                     "batch_per_client": BATCH, "fl_config": "G1 (torch.cuda.amp.autocast fp16 + GradScaler)",
+                     "step": "one FL round = 50 local steps + Bcast + Allreduce",
+                     "windows_per_client": args.num_windows,
+                     "timing": "reference's own perf_counter brackets (every step ends in cuda.synchronize), "
+                               "local_train_ms + comm_ms summed over timed rounds, max over ranks",
+                     "mpi": "mpi4py shim over torch.distributed gloo (host buffers), torchrun launch"},
+          "exposed_agg_ms_per_round": comm_ms, "clocks": clocks,
+          "e2e": {"value": value, "unit": "samples/s", "h2d_bytes_per_step": 0,
+                  "d2h_bytes_per_step": 4 * LOCAL_STEPS + 2 * 5832,
+                  "note": "reference keeps its dataset GPU-resident; per round it reads loss.item() every step and "
+                          "stages all parameters D2H+H2D twice"},
+          "gpu_launches": None})
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

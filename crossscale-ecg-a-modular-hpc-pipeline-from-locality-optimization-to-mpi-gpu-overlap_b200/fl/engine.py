@@ -1,0 +1,380 @@
+"""Local-step engines and the FedAvg round loop.
+
+Parity map:
+  * ``train_step_G0`` / ``train_step_G1``      ``TRUE_FL_M3/part3_fedavg_overlap_mpi_gpu.py:103-132``
+  * ``run_baseline_gpu`` / ``run_overlap_gpu``  ``Module_3/part3_mpi_gpu_train.py:100-184, 306-412``
+  * ``FedAvgRunner.run``                         round loop of ``part3_fedavg...py:186-231``
+
+B200 design: on CUDA a TinyECG local step is ONE kernel (``ops.tiny_ecg``), a round's
+``local_steps`` launches are captured once in a CUDA graph and replayed, the loss is accumulated on
+the device and read back once per round, and aggregation is one in-kernel NVLink collective
+(``parallel.fedavg``).  The reference's per-step ``cuda.synchronize()`` + ``loss.item()`` are gone.
+On CPU (no GPU) everything runs through stock PyTorch — that path is the plumbing config of
+``BASELINE.json`` and the numerical oracle of the GPU tests.
+"""
+from __future__ import annotations
+
+import time
+from dataclasses import asdict
+from typing import Callable, Dict, Iterator, List, Optional, Tuple
+
+import torch
+import torch.nn.functional as F
+
+from ..models.tiny_ecg import TinyECG
+from ..ops import tiny_ecg as tk
+from ..parallel.fedavg import FedAvgAggregator, broadcast_model, client_weight
+from .stats import BenchStats, RoundStatsExt
+
+G0_LABEL, G1_LABEL = "G0_baseline_GPU_CACHE", "G1_overlap_amp"
+
+
+# ---------------------------------------------------------------------------------------------
+# reference-shaped step functions (work on any nn.Module, CPU or CUDA)
+# ---------------------------------------------------------------------------------------------
+def train_step_G0(model, x, y, opt, device) -> float:
+    model.train()
+    opt.zero_grad(set_to_none=True)
+    loss = F.cross_entropy(model(x), y)
+    loss.backward()
+    opt.step()
+    if torch.device(device).type == "cuda":
+        torch.cuda.synchronize()
+    return float(loss.item())
+
+
+def train_step_G1(model, x, y, opt, scaler, device, dtype: torch.dtype = torch.float16) -> float:
+    model.train()
+    opt.zero_grad(set_to_none=True)
+    dev_type = torch.device(device).type
+    with torch.autocast(device_type=dev_type, dtype=dtype if dev_type == "cuda" else torch.bfloat16):
+        loss = F.cross_entropy(model(x), y)
+    if scaler is not None:
+        scaler.scale(loss).backward()
+        scaler.step(opt)
+        scaler.update()
+    else:
+        loss.backward()
+        opt.step()
+    if dev_type == "cuda":
+        torch.cuda.synchronize()
+    return float(loss.item())
+
+
+# ---------------------------------------------------------------------------------------------
+# index stream: the permutation-batch order of make_gpu_batch_iter, produced a round at a time
+# ---------------------------------------------------------------------------------------------
+class IndexStream:
+    """Per-epoch ``randperm(N)``, ragged tail dropped, handed out ``steps*B`` indices at a time."""
+
+    def __init__(self, n: int, batch: int, device, generator: Optional[torch.Generator] = None):
+        if n < batch:
+            raise ValueError(f"dataset has {n} windows < batch {batch}")
+        self.n, self.batch, self.device, self.gen = n, batch, device, generator
+        self.usable = (n // batch) * batch
+        self.perm = None
+        self.pos = 0
+
+    def fill(self, out: torch.Tensor) -> None:
+        need, done = out.numel(), 0
+        while done < need:
+            if self.perm is None or self.pos >= self.usable:
+                self.perm = torch.randperm(self.n, device=self.device, generator=self.gen)
+                self.pos = 0
+            take = min(need - done, self.usable - self.pos)
+            out[done:done + take].copy_(self.perm[self.pos:self.pos + take])
+            done += take
+            self.pos += take
+
+
+# ---------------------------------------------------------------------------------------------
+# trainers
+# ---------------------------------------------------------------------------------------------
+class TorchLocalTrainer:
+    """Stock-PyTorch local training (CPU plumbing config, oracle, and non-TinyECG models)."""
+
+    def __init__(self, model: torch.nn.Module, device, lr=1e-2, momentum=0.9, amp: str = "none"):
+        self.model, self.device, self.amp = model, torch.device(device), amp
+        self.opt = torch.optim.SGD(model.parameters(), lr=lr, momentum=momentum)
+        self.scaler = None
+        if amp == "fp16" and self.device.type == "cuda":
+            self.scaler = torch.amp.GradScaler("cuda")
+        self.launches = 0
+
+    def flat_parameters(self) -> torch.Tensor:
+        return torch.cat([p.detach().reshape(-1) for p in self.model.parameters()])
+
+    def load_flat(self, flat: torch.Tensor) -> None:
+        off = 0
+        with torch.no_grad():
+            for p in self.model.parameters():
+                n = p.numel()
+                p.copy_(flat[off:off + n].view_as(p))
+                off += n
+
+    def run_steps(self, batch_iter: Iterator, steps: int) -> Tuple[float, int]:
+        loss_acc, n = 0.0, 0
+        for _ in range(steps):
+            x, y = next(batch_iter)
+            n += x.size(0)
+            if self.amp == "none":
+                loss_acc += train_step_G0(self.model, x, y, self.opt, self.device)
+            else:
+                dt = torch.float16 if self.amp == "fp16" else torch.bfloat16
+                loss_acc += train_step_G1(self.model, x, y, self.opt, self.scaler, self.device, dt)
+        return loss_acc, n
+
+
+class FusedTinyTrainer:
+    """TinyECG local training with the one-launch step kernel + CUDA-graph replay."""
+
+    def __init__(self, model: TinyECG, x_gpu: torch.Tensor, y_gpu: torch.Tensor, batch: int,
+                 local_steps: int, lr=1e-2, momentum=0.9, amp: str = "none", use_graph: bool = True,
+                 generator: Optional[torch.Generator] = None):
+        assert x_gpu.is_cuda and x_gpu.dim() == 2
+        self.model, self.batch, self.local_steps = model, batch, local_steps
+        self.flat = model.flatten_parameters()
+        amp_code = tk.AMP_BY_NAME[amp]
+        self.state = tk.TinyTrainState(self.flat.flat, model.num_classes, lr=lr, momentum=momentum,
+                                       amp=amp_code, scaler=tk.ScalerConfig(enabled=(amp == "fp16")))
+        self.x, self.y = x_gpu, y_gpu
+        self.stream_idx = IndexStream(x_gpu.shape[0], batch, x_gpu.device, generator)
+        self.idx = torch.zeros(local_steps * batch, dtype=torch.int64, device=x_gpu.device)
+        self.use_graph, self.graph, self._warm = use_graph, None, False
+        self.launches = 0
+
+    def _resident_steps(self):
+        b = self.batch
+        for s in range(self.local_steps):
+            self.state.step(self.x, self.y, self.idx[s * b:(s + 1) * b], batch=b)
+
+    def run_round_resident(self) -> None:
+        """``local_steps`` fused steps over the GPU-resident dataset (asynchronous)."""
+        self.stream_idx.fill(self.idx)
+        if not self.use_graph or not self._warm:
+            self._resident_steps()                 # first round runs eagerly (one-time kernel set-up)
+            self._warm = True
+        else:
+            if self.graph is None:
+                self.graph = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(self.graph):
+                    self._resident_steps()
+            self.graph.replay()
+        self.launches += self.local_steps
+
+    def run_round_staged(self, xb: torch.Tensor, yb: torch.Tensor) -> None:
+        """``local_steps`` fused steps over a staged device buffer ``[steps*B, L]`` (fp32 or bf16)."""
+        b = self.batch
+        for s in range(self.local_steps):
+            self.state.step(xb[s * b:(s + 1) * b], yb[s * b:(s + 1) * b], None, batch=b)
+        self.launches += self.local_steps
+
+    def flat_parameters(self) -> torch.Tensor:
+        return self.flat.flat
+
+
+# ---------------------------------------------------------------------------------------------
+# pseudo-federated engines (no parameter exchange): BenchStats rows
+# ---------------------------------------------------------------------------------------------
+def _bench_row(config, world, rank, batch, steps, data_ms, h2d_ms, compute_ms) -> dict:
+    step_ms = (data_ms + h2d_ms + compute_ms) / max(steps, 1)
+    return asdict(BenchStats(config=config, world_size=world, rank=rank, batch_size=batch, steps=steps,
+                             data_ms=data_ms / max(steps, 1), h2d_ms=h2d_ms / max(steps, 1),
+                             compute_ms=compute_ms / max(steps, 1), step_ms=step_ms,
+                             samples_per_s=batch / (step_ms / 1e3) if step_ms > 0 else 0.0))
+
+
+def _run_pseudo(model, batch_iter, device, steps, rank, batch_size, world, amp, label, x_gpu=None, y_gpu=None):
+    device = torch.device(device)
+    fused = (device.type == "cuda" and isinstance(model, TinyECG) and tk.use_kernels()
+             and x_gpu is not None and model.num_classes <= tk.MAX_CLASSES)
+    if fused:
+        chunk = min(steps, 50)
+        tr = FusedTinyTrainer(model, x_gpu, y_gpu, batch_size, chunk, amp=amp)
+        tr.run_round_resident()                       # warm-up + graph capture, not timed
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        done, a_rec = 0, False
+        while done < steps:
+            if not a_rec:
+                a.record(); a_rec = True
+            tr.run_round_resident()
+            done += chunk
+            if rank == 0 and done % 10 == 0:
+                pass
+        b.record()
+        torch.cuda.synchronize()
+        return _bench_row(label, world, rank, batch_size, done, 0.0, 0.0, a.elapsed_time(b))
+    tr = TorchLocalTrainer(model, device, amp=amp)
+    t0 = time.perf_counter()
+    for s in range(steps):
+        if rank == 0 and s % 10 == 0:
+            print(f"[{label}] step {s}/{steps}", flush=True)
+        tr.run_steps(batch_iter, 1)
+    if device.type == "cuda":
+        torch.cuda.synchronize()
+    return _bench_row(label, world, rank, batch_size, steps, 0.0, 0.0, (time.perf_counter() - t0) * 1e3)
+
+
+def run_baseline_gpu(model, batch_iter, device, steps, rank, batch_size, world_size=1, x_gpu=None, y_gpu=None):
+    """G0: fp32 local training, data GPU-resident.  Returns a ``BenchStats`` dict."""
+    return _run_pseudo(model, batch_iter, device, steps, rank, batch_size, world_size, "none", G0_LABEL, x_gpu, y_gpu)
+
+
+def run_overlap_gpu(model, batch_iter, device, steps, rank, batch_size, world_size=1, x_gpu=None, y_gpu=None,
+                    amp: str = "bf16"):
+    """G1: AMP local training (bf16 by default; ``amp='fp16'`` adds the loss scaler)."""
+    return _run_pseudo(model, batch_iter, device, steps, rank, batch_size, world_size, amp, G1_LABEL, x_gpu, y_gpu)
+
+
+# ---------------------------------------------------------------------------------------------
+# FedAvg round loop
+# ---------------------------------------------------------------------------------------------
+class FedAvgRunner:
+    """One client's view of FedAvg training (SPMD: every rank runs one of these)."""
+
+    def __init__(self, model: torch.nn.Module, device, x_gpu: torch.Tensor, y_gpu: torch.Tensor,
+                 batch_size: int = 256, local_steps: int = 50, config: str = "G0", amp: str = "auto",
+                 rank: int = 0, world: int = 1, lr: float = 1e-2, momentum: float = 0.9,
+                 agg_backend: str = "auto", wire: str = "fp32", server_lr: float = 1.0,
+                 reset_momentum: bool = False, use_graph: bool = True,
+                 generator: Optional[torch.Generator] = None, model_name: str = "tiny_ecg"):
+        self.device = torch.device(device)
+        self.model, self.rank, self.world = model, rank, world
+        self.batch, self.local_steps, self.config = batch_size, local_steps, config
+        if amp == "auto":
+            amp = "none" if config == "G0" else "bf16"
+        self.amp, self.model_name = amp, model_name
+        self.fused = (self.device.type == "cuda" and isinstance(model, TinyECG) and tk.use_kernels()
+                      and model.num_classes <= tk.MAX_CLASSES)
+        if self.fused:
+            self.trainer = FusedTinyTrainer(model, x_gpu, y_gpu, batch_size, local_steps, lr, momentum,
+                                            amp, use_graph, generator)
+            self.flat = self.trainer.flat.flat
+            self.numel = self.trainer.flat.numel
+            self.mom = self.trainer.state.mom
+            self.batch_iter = None
+        else:
+            from ..data.shard_dataset import make_gpu_batch_iter
+            self.trainer = TorchLocalTrainer(model, self.device, lr, momentum,
+                                             amp if self.device.type == "cuda" else "none")
+            self.batch_iter = make_gpu_batch_iter(x_gpu, y_gpu, batch_size, generator)
+            self.flat = self.trainer.flat_parameters()
+            self.numel = self.flat.numel()
+            self.mom = None
+        self.weight = client_weight(x_gpu.shape[0], self.device)
+        broadcast_model(self.flat)                       # round 0: common initial model
+        if not self.fused:
+            self.trainer.load_flat(self.flat)
+        self.prev = self.flat.clone()
+        self.agg = FedAvgAggregator(self.numel, self.device, backend=agg_backend, wire=wire,
+                                    server_lr=server_lr, reset_momentum=reset_momentum)
+        self.rows: List[dict] = []
+
+    def _events(self):
+        return [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+
+    def run_round(self, round_idx: int, record: bool = True) -> dict:
+        cuda = self.device.type == "cuda"
+        n_samples = self.local_steps * self.batch
+        if cuda:
+            e0, e1, e2 = self._events()
+            e0.record()
+        t0 = time.perf_counter()
+        if self.fused:
+            self.trainer.state.reset_loss()
+            self.trainer.run_round_resident()
+        else:
+            loss_acc, n_samples = self.trainer.run_steps(self.batch_iter, self.local_steps)
+            self.flat = self.trainer.flat_parameters()
+        t1 = time.perf_counter()
+        if cuda:
+            e1.record()
+        self.agg.aggregate(self.flat, self.prev, self.weight, self.mom)
+        if not self.fused:
+            self.trainer.load_flat(self.flat)
+        if cuda:
+            e2.record()
+            torch.cuda.synchronize()
+            local_ms, comm_ms = e0.elapsed_time(e1), e1.elapsed_time(e2)
+        else:
+            t2 = time.perf_counter()
+            local_ms, comm_ms = (t1 - t0) * 1e3, (t2 - t1) * 1e3
+        avg_loss = (self.trainer.state.loss_sum() if self.fused else loss_acc) / self.local_steps
+        row = asdict(RoundStatsExt(
+            config=self.config, world_size=self.world, rank=self.rank, round_idx=round_idx,
+            batch_size=self.batch, local_steps=self.local_steps, local_train_ms=local_ms, comm_ms=comm_ms,
+            samples_per_s=n_samples / (local_ms / 1e3) if local_ms > 0 else 0.0, avg_loss=avg_loss,
+            round_ms_dev=local_ms + comm_ms, agg_ms_dev=comm_ms, exposed_agg_ms=comm_ms,
+            amp=self.amp, model=self.model_name))
+        if record:
+            self.rows.append(row)
+        return row
+
+    def run(self, rounds: int) -> List[dict]:
+        for r in range(rounds):
+            self.run_round(r)
+        return self.rows
+
+    # -- asynchronous round (device-timed benchmarks): nothing here synchronises the host -------
+    def run_round_async(self) -> None:
+        assert self.fused, "async rounds need the fused CUDA trainer"
+        self.trainer.run_round_resident()
+        self.agg.aggregate(self.flat, self.prev, self.weight, self.mom)
+
+    # -- end-to-end round: pinned-host block -> H2D on the copy stream -> train -> aggregate ->
+    #    loss read back to the host (the call a user makes when data does not live on the GPU) ---
+    def enable_e2e(self, store, seed: int = 0) -> None:
+        from ..data.staging import BlockSampler, H2DStager
+        from ..ops import _lib
+        assert self.fused, "the staged end-to-end path needs the fused CUDA trainer"
+        rows = self.local_steps * self.batch
+        self._store, self._sampler = store, BlockSampler(store.n, rows, seed)
+        self._stager = H2DStager(rows, store.l, store.x.dtype, self.device)
+        self._loss_host = torch.zeros(8, dtype=torch.float32, pin_memory=True)
+        self._loss_prev = 0.0
+        self._graphs = [None, None]
+        self._slot = 0
+        self._lib = _lib
+        self.d2h_bytes = 4
+        self._stage_next(0)
+
+    def _stage_next(self, slot: int) -> None:
+        hx, hy = self._store.block(self._sampler.next_start(), self.local_steps * self.batch)
+        self._stager.stage(slot, hx, hy)
+
+    def run_round_e2e(self) -> float:
+        """One FL round fed from pinned host memory; returns the round's mean loss (host float)."""
+        slot = self._slot
+        xb, yb = self._stager.acquire(slot)
+        self._stage_next(slot ^ 1)                  # next block's H2D overlaps this round's compute
+        tr = self.trainer
+        if not tr.use_graph:
+            tr.run_round_staged(xb, yb)
+        else:
+            if self._graphs[slot] is None:
+                tr.run_round_staged(xb, yb)         # eager once (also the first round's work)
+                g = torch.cuda.CUDAGraph()
+                self._graphs[slot] = (g, xb, yb)
+            else:
+                g = self._graphs[slot][0]
+                if not getattr(g, "_cs_captured", False):
+                    with torch.cuda.graph(g):
+                        tr.run_round_staged(xb, yb)
+                    g._cs_captured = True
+                g.replay()
+                tr.launches += self.local_steps
+        self._stager.release(slot)
+        self.agg.aggregate(self.flat, self.prev, self.weight, self.mom)
+        st = torch.cuda.current_stream(self.device)
+        self._lib.check(self._lib.cuda_lib().cs_stage_d2h(self._loss_host.data_ptr(), tr.state.fstate.data_ptr(),
+                                                          4, st.cuda_stream), "cs_stage_d2h")
+        st.synchronize()
+        total = float(self._loss_host[0])
+        loss = (total - self._loss_prev) / self.local_steps
+        self._loss_prev = total
+        self._slot ^= 1
+        return loss
+
+    def close(self):
+        self.agg.close()

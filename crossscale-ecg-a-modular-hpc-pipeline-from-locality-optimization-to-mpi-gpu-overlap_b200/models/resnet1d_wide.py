@@ -1,0 +1,63 @@
+"""Widened ResNet-1D ECG classifier (~24 M parameters at the default widths).
+
+Not in the reference; it is the bandwidth-bound aggregation stress model named by
+``BASELINE.json`` ("Widened ResNet-1D ECG model (~25M params) FedAvg over 8xB200").  Convolutions go
+through ``ops.conv1d`` (tcgen05 implicit GEMM on CUDA, ``F.conv1d`` on CPU); BN + ReLU (+ residual)
+go through ``ops.norm_act`` which is one fused kernel on CUDA.
+"""
+from __future__ import annotations
+
+from typing import Sequence
+
+import torch
+import torch.nn as nn
+
+from ..ops.conv1d import Conv1dB200
+from ..ops.norm_act import BNReLU1d, global_avg_pool1d
+
+
+class BasicBlock1D(nn.Module):
+    def __init__(self, cin: int, cout: int, k: int = 7, stride: int = 1):
+        super().__init__()
+        self.conv1 = Conv1dB200(cin, cout, k, padding=k // 2, stride=stride, bias=False)
+        self.bn1 = BNReLU1d(cout, relu=True)
+        self.conv2 = Conv1dB200(cout, cout, k, padding=k // 2, bias=False)
+        self.bn2 = BNReLU1d(cout, relu=True)  # ReLU applied after the residual add (fused)
+        self.down = None
+        if cin != cout or stride != 1:
+            self.down = Conv1dB200(cin, cout, 1, padding=0, stride=stride, bias=False)
+            self.down_bn = BNReLU1d(cout, relu=False)
+
+    def forward(self, x):
+        idn = x if self.down is None else self.down_bn(self.down(x))
+        y = self.bn1(self.conv1(x))
+        return self.bn2(self.conv2(y), residual=idn)
+
+
+class ResNet1DWide(nn.Module):
+    def __init__(self, num_classes: int = 5, widths: Sequence[int] = (128, 256, 512, 768),
+                 blocks_per_stage: int = 2, stem: int = 64, k: int = 7):
+        super().__init__()
+        self.stem = Conv1dB200(1, stem, 7, padding=3, bias=False)
+        self.stem_bn = BNReLU1d(stem, relu=True)
+        layers, cin = [], stem
+        for i, w in enumerate(widths):
+            for b in range(blocks_per_stage):
+                layers.append(BasicBlock1D(cin, w, k=k, stride=2 if (b == 0 and i > 0) else 1))
+                cin = w
+        self.layers = nn.Sequential(*layers)
+        self.head = nn.Linear(cin, num_classes)
+
+    def forward(self, x):
+        y = self.stem_bn(self.stem(x))
+        y = self.layers(y)
+        return self.head(global_avg_pool1d(y))
+
+
+def resnet1d_wide_25m(num_classes: int = 5) -> ResNet1DWide:
+    return ResNet1DWide(num_classes=num_classes)
+
+
+def resnet1d_small(num_classes: int = 5) -> ResNet1DWide:
+    """Small variant for tests."""
+    return ResNet1DWide(num_classes=num_classes, widths=(16, 32), blocks_per_stage=1, stem=16, k=5)

@@ -1,0 +1,108 @@
+"""Symmetric peer memory: one arena + signal pad per rank, mapped into every peer (CUDA IPC).
+
+This is the bootstrap layer under the in-kernel collectives: the only host-side
+communication is the one-time exchange of two 64-byte IPC handles per rank through the
+``torch.distributed`` store/gloo/nccl object collectives — the hot paths never call MPI or NCCL.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import List, Optional
+
+import torch
+import torch.distributed as dist
+
+from ..ops import _lib
+
+HANDLE_BYTES = 64
+
+
+class SymmetricComm:
+    """A communicator over peer-mapped arenas (real multi-process, one GPU per rank)."""
+
+    def __init__(self, arena_bytes: int, group: Optional[dist.ProcessGroup] = None):
+        lib = _lib.cuda_lib()
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self._h = C.c_void_p()
+        ah = (C.c_char * HANDLE_BYTES)()
+        sh = (C.c_char * HANDLE_BYTES)()
+        _lib.check(lib.cs_comm_create(self.rank, self.world, int(arena_bytes), C.byref(self._h), ah, sh),
+                   "cs_comm_create")
+        if self.world > 1:
+            gathered: List = [None] * self.world
+            dist.all_gather_object(gathered, (bytes(ah.raw), bytes(sh.raw)), group=group)
+            ahs = b"".join(g[0] for g in gathered)
+            shs = b"".join(g[1] for g in gathered)
+            _lib.check(lib.cs_comm_connect(self._h, ahs, shs), "cs_comm_connect")
+            dist.barrier(group=group)  # every rank has mapped every peer before first use
+        self.arena_bytes = int(lib.cs_comm_arena_bytes(self._h))
+        self.emulated = False
+
+    @property
+    def handle(self):
+        return self._h
+
+    def barrier(self, channel: int = 0) -> None:
+        _lib.check(_lib.cuda_lib().cs_comm_barrier(self._h, channel, _lib.stream_ptr()), "cs_comm_barrier")
+
+    def status(self) -> int:
+        out = C.c_int(0)
+        _lib.check(_lib.cuda_lib().cs_comm_status(self._h, C.byref(out)), "cs_comm_status")
+        return out.value
+
+    def close(self) -> None:
+        if self._h:
+            torch.cuda.synchronize()
+            _lib.cuda_lib().cs_comm_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):  # pragma: no cover
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class LocalGroup:
+    """``world`` emulated ranks on ONE device; every collective is one cooperative launch.
+
+    Used by single-GPU tests and the 1-GPU multi-client simulation: the same kernels run with
+    ``blockIdx.y`` as the rank, so the peer-pointer / flag protocol is exercised without peers.
+    """
+
+    def __init__(self, world: int, arena_bytes: int):
+        lib = _lib.cuda_lib()
+        self.world = world
+        self._arr = (C.c_void_p * world)()
+        _lib.check(lib.cs_comm_create_local(world, int(arena_bytes), self._arr), "cs_comm_create_local")
+        self.arena_bytes = int(lib.cs_comm_arena_bytes(self._arr[0]))
+        self.emulated = True
+
+    @property
+    def handles(self):
+        return self._arr
+
+    def barrier(self, channel: int = 0) -> None:
+        _lib.check(_lib.cuda_lib().cs_comm_barrier(self._arr[0], channel, _lib.stream_ptr()), "cs_comm_barrier")
+
+    def status(self) -> int:
+        out = C.c_int(0)
+        worst = 0
+        for r in range(self.world):
+            _lib.check(_lib.cuda_lib().cs_comm_status(self._arr[r], C.byref(out)), "cs_comm_status")
+            worst = max(worst, out.value)
+        return worst
+
+    def close(self) -> None:
+        if self._arr is not None and self._arr[0]:
+            torch.cuda.synchronize()
+            _lib.cuda_lib().cs_comm_destroy(self._arr[0])
+            self._arr = None
+
+
+def ptr_array(tensors) -> "C.Array":
+    arr = (C.c_void_p * len(tensors))()
+    for i, t in enumerate(tensors):
+        arr[i] = None if t is None else t.data_ptr()
+    return arr

@@ -1,0 +1,239 @@
+// extern "C" surface of libcrossscale_cuda.so (declared in include/crossscale.h).
+#include "tiny_ecg.cuh"
+
+#include <stdarg.h>
+#include <string.h>
+
+struct cs_comm;
+
+namespace cs {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+int fail(cudaError_t e, const char* what) {
+    set_error("CUDA error %d (%s) at %s", (int)e, cudaGetErrorString(e), what);
+    cudaGetLastError();   // clear the sticky-less error state
+    return CS_ERR_CUDA;
+}
+
+int num_sms() {
+    static int cached[64] = {0};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+    if (cached[dev] == 0) {
+        int n = 0;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+        cached[dev] = n;
+    }
+    return cached[dev];
+}
+
+// implemented in the other translation units
+int gather_rows(const float*, const int64_t*, const int64_t*, void*, int64_t*, int, int, int, cudaStream_t);
+int cross_entropy(const float*, const int64_t*, int, int, const float*, float*, float*, cudaStream_t);
+int sgd_momentum(float*, float*, const float*, int64_t, float, float, float, int, int32_t*, float*, float, float, int, void*, cudaStream_t);
+int zscore_rows(const float*, void*, int, int, int, cudaStream_t);
+int bn_stats(const void*, float*, int64_t, int, cudaStream_t);
+int bn_apply(const void*, const void*, void*, const float*, const float*, const float*, const float*, int64_t, int, int, cudaStream_t);
+int bn_bwd_reduce(const void*, const void*, const void*, const float*, const float*, float*, float*, int64_t, int, int, cudaStream_t);
+int bn_bwd_apply(const void*, const void*, const void*, const float*, const float*, const float*, const float*, const float*, void*, void*, int64_t, int, int, cudaStream_t);
+int avgpool_fwd(const void*, float*, int, int, int, cudaStream_t);
+int avgpool_bwd(const float*, void*, int, int, int, cudaStream_t);
+int ncl_to_nlc(const float*, void*, int, int, int, cudaStream_t);
+int nlc_to_ncl(const void*, float*, int, int, int, cudaStream_t);
+
+int comm_create(int, int, size_t, cs_comm**, void*, void*);
+int comm_connect(cs_comm*, const void*, const void*);
+int comm_create_local(int, size_t, cs_comm**);
+int comm_destroy(cs_comm*);
+int comm_barrier(cs_comm*, int, cudaStream_t);
+int comm_status(cs_comm*, int*);
+size_t agg_arena_need(long long, int, int);
+int fedavg_aggregate(cs_comm*, float*, float*, long long, float, int, float, float*, size_t, int, float, cudaStream_t);
+int fedavg_aggregate_local(cs_comm**, int, float* const*, float* const*, long long, const float*, int, float,
+                           float* const*, size_t, int, float, cudaStream_t);
+void* comm_arena(cs_comm*, int);
+size_t comm_bytes(cs_comm*);
+
+int conv1d_fwd(const void*, const void*, const float*, void*, int, int, int, int, int, int, int, int, cudaStream_t);
+int conv1d_prepare_dgrad_weight(const void*, void*, int, int, int, cudaStream_t);
+int conv1d_wgrad(const void*, const void*, float*, float*, int, int, int, int, int, int, int, cudaStream_t);
+int conv1d_cin1_fwd(const float*, const float*, const float*, void*, int, int, int, int, int, int, int, cudaStream_t);
+int conv1d_cin1_wgrad(const float*, const void*, float*, float*, int, int, int, int, int, int, cudaStream_t);
+
+static TinyArgs make_args(const void* x, const int64_t* y, const int64_t* idx, int x_bf16, int B, int L, int C, int amp) {
+    TinyArgs a;
+    memset(&a, 0, sizeof(a));
+    a.x = x; a.y = y; a.idx = idx; a.x_bf16 = x_bf16; a.B = B; a.L = L; a.C = C; a.amp = amp;
+    return a;
+}
+
+static bool use_umma(int amp, int L, int C) {
+    return amp != CS_AMP_FP32 && tiny_umma_supported(L, C);
+}
+
+}  // namespace cs
+
+using namespace cs;
+#define ST(s) ((cudaStream_t)(s))
+
+extern "C" {
+
+const char* cs_last_error(void) { return g_err; }
+int cs_version(void) { return 100; }
+
+int cs_device_is_sm100(void) {
+    int dev = 0, major = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return 0;
+    if (cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev) != cudaSuccess) return 0;
+    return major == 10;
+}
+
+int cs_gather_rows(const float* x, const int64_t* y, const int64_t* idx, void* xo, int64_t* yo, int B, int L,
+                   int out_bf16, cs_stream_t s) {
+    return gather_rows(x, y, idx, xo, yo, B, L, out_bf16, ST(s));
+}
+
+size_t cs_tiny_ecg_smem_bytes(int L, int C, int amp) {
+    return use_umma(amp, L, C) ? tiny_umma_smem_bytes(L, C) : tiny_f32_smem_bytes(L, C);
+}
+
+int cs_tiny_ecg_forward(const void* x, const int64_t* idx, int x_bf16, int B, int L, int C, const float* params,
+                        float* logits, int amp, cs_stream_t s) {
+    TinyArgs a = make_args(x, nullptr, idx, x_bf16, B, L, C, amp);
+    a.params = const_cast<float*>(params); a.logits = logits;
+    return use_umma(amp, L, C) ? tiny_umma_forward(a, ST(s)) : tiny_f32_forward(a, ST(s));
+}
+
+int cs_tiny_ecg_backward(const void* x, const int64_t* idx, int x_bf16, int B, int L, int C, const float* params,
+                         const float* dlogits, float* grad, int amp, cs_stream_t s) {
+    TinyArgs a = make_args(x, nullptr, idx, x_bf16, B, L, C, amp);
+    a.params = const_cast<float*>(params); a.dlogits = dlogits; a.gacc = grad;
+    return use_umma(amp, L, C) ? tiny_umma_backward(a, ST(s)) : tiny_f32_backward(a, ST(s));
+}
+
+int cs_tiny_ecg_train_step(const void* x, const int64_t* y, const int64_t* idx, int x_bf16, int B, int L, int C,
+                           float* params, float* mom, float* gacc, int32_t* ctrl, float* fstate, float lr,
+                           float momentum, float wd, int amp, int use_scaler, float growth, float backoff,
+                           int growth_interval, cs_stream_t s) {
+    CS_REQUIRE(y != nullptr && params && mom && gacc && ctrl && fstate, "train_step: null state pointer");
+    TinyArgs a = make_args(x, y, idx, x_bf16, B, L, C, amp);
+    a.params = params; a.mom = mom; a.gacc = gacc; a.ctrl = ctrl; a.fstate = fstate;
+    a.lr = lr; a.momentum = momentum; a.wd = wd; a.use_scaler = use_scaler;
+    a.growth = growth; a.backoff = backoff; a.interval = growth_interval;
+    return use_umma(amp, L, C) ? tiny_umma_train(a, ST(s)) : tiny_f32_train(a, ST(s));
+}
+
+int cs_cross_entropy_fwd_bwd(const float* logits, const int64_t* y, int B, int C, const float* scale_ptr,
+                             float* loss_out, float* dlogits, cs_stream_t s) {
+    return cross_entropy(logits, y, B, C, scale_ptr, loss_out, dlogits, ST(s));
+}
+
+int cs_sgd_momentum(float* p, float* mom, const float* g, int64_t n, float lr, float momentum, float wd,
+                    int use_scaler, int32_t* ctrl, float* fstate, float growth, float backoff, int interval,
+                    void* shadow, cs_stream_t s) {
+    return sgd_momentum(p, mom, g, n, lr, momentum, wd, use_scaler, ctrl, fstate, growth, backoff, interval, shadow, ST(s));
+}
+
+int cs_conv1d_fwd(const void* x, const void* w, const float* bias, void* y, int B, int L, int Cin, int Cout, int K,
+                  int pad, int stride, int relu, cs_stream_t s) {
+    return conv1d_fwd(x, w, bias, y, B, L, Cin, Cout, K, pad, stride, relu, ST(s));
+}
+int cs_conv1d_dgrad(const void* dy, const void* wt, void* dx, int B, int L, int Cin, int Cout, int K, int pad,
+                    int stride, cs_stream_t s) {
+    // dgrad of a stride-1 conv is a stride-1 conv of dy with the flipped/transposed filter and
+    // padding K-1-pad; Lout == L for "same" padding.
+    CS_REQUIRE(stride == 1, "conv1d_dgrad: stride %d not supported by the implicit-GEMM path", stride);
+    const int Lout = L + 2 * pad - K + 1;
+    return conv1d_fwd(dy, wt, nullptr, dx, B, Lout, Cout, Cin, K, K - 1 - pad, 1, 0, ST(s));
+}
+int cs_conv1d_prepare_dgrad_weight(const void* w, void* wt, int K, int Cout, int Cin, cs_stream_t s) {
+    return conv1d_prepare_dgrad_weight(w, wt, K, Cout, Cin, ST(s));
+}
+int cs_conv1d_wgrad(const void* x, const void* dy, float* dw, float* dbias, int B, int L, int Cin, int Cout, int K,
+                    int pad, int stride, cs_stream_t s) {
+    return conv1d_wgrad(x, dy, dw, dbias, B, L, Cin, Cout, K, pad, stride, ST(s));
+}
+int cs_conv1d_cin1_fwd(const float* x, const float* w, const float* bias, void* y, int B, int L, int Cout, int K,
+                       int pad, int stride, int relu, cs_stream_t s) {
+    return conv1d_cin1_fwd(x, w, bias, y, B, L, Cout, K, pad, stride, relu, ST(s));
+}
+int cs_conv1d_cin1_wgrad(const float* x, const void* dy, float* dw, float* dbias, int B, int L, int Cout, int K,
+                         int pad, int stride, cs_stream_t s) {
+    return conv1d_cin1_wgrad(x, dy, dw, dbias, B, L, Cout, K, pad, stride, ST(s));
+}
+
+int cs_bn_stats(const void* x, float* stats, int64_t rows, int C, cs_stream_t s) { return bn_stats(x, stats, rows, C, ST(s)); }
+int cs_bn_apply(const void* x, const void* res, void* y, const float* mean, const float* rstd, const float* gamma,
+                const float* beta, int64_t rows, int C, int relu, cs_stream_t s) {
+    return bn_apply(x, res, y, mean, rstd, gamma, beta, rows, C, relu, ST(s));
+}
+int cs_bn_bwd_reduce(const void* x, const void* y, const void* dy, const float* mean, const float* rstd, float* dgamma,
+                     float* dbeta, int64_t rows, int C, int relu, cs_stream_t s) {
+    return bn_bwd_reduce(x, y, dy, mean, rstd, dgamma, dbeta, rows, C, relu, ST(s));
+}
+int cs_bn_bwd_apply(const void* x, const void* y, const void* dy, const float* mean, const float* rstd,
+                    const float* gamma, const float* dgamma, const float* dbeta, void* dx, void* dres, int64_t rows,
+                    int C, int relu, cs_stream_t s) {
+    return bn_bwd_apply(x, y, dy, mean, rstd, gamma, dgamma, dbeta, dx, dres, rows, C, relu, ST(s));
+}
+int cs_avgpool_fwd(const void* x, float* out, int B, int L, int C, cs_stream_t s) { return avgpool_fwd(x, out, B, L, C, ST(s)); }
+int cs_avgpool_bwd(const float* dout, void* dx, int B, int L, int C, cs_stream_t s) { return avgpool_bwd(dout, dx, B, L, C, ST(s)); }
+int cs_ncl_f32_to_nlc_bf16(const float* x, void* y, int B, int C, int L, cs_stream_t s) { return ncl_to_nlc(x, y, B, C, L, ST(s)); }
+int cs_nlc_bf16_to_ncl_f32(const void* x, float* y, int B, int C, int L, cs_stream_t s) { return nlc_to_ncl(x, y, B, C, L, ST(s)); }
+
+int cs_comm_create(int rank, int world, size_t bytes, cs_comm_t** out, void* ah, void* sh) {
+    return comm_create(rank, world, bytes, (cs_comm**)out, ah, sh);
+}
+int cs_comm_connect(cs_comm_t* c, const void* ahs, const void* shs) { return comm_connect((cs_comm*)c, ahs, shs); }
+int cs_comm_create_local(int world, size_t bytes, cs_comm_t** out) { return comm_create_local(world, bytes, (cs_comm**)out); }
+void* cs_comm_arena(cs_comm_t* c) { return comm_arena((cs_comm*)c, -1); }
+void* cs_comm_peer_arena(cs_comm_t* c, int r) { return comm_arena((cs_comm*)c, r); }
+size_t cs_comm_arena_bytes(cs_comm_t* c) { return comm_bytes((cs_comm*)c); }
+int cs_comm_destroy(cs_comm_t* c) { return comm_destroy((cs_comm*)c); }
+int cs_comm_barrier(cs_comm_t* c, int channel, cs_stream_t s) { return comm_barrier((cs_comm*)c, channel, ST(s)); }
+int cs_comm_status(cs_comm_t* c, int* out) { return comm_status((cs_comm*)c, out); }
+size_t cs_fedavg_arena_bytes(int64_t n, int wire_bf16, int world) { return agg_arena_need(n, wire_bf16, world); }
+
+int cs_fedavg_aggregate(cs_comm_t* c, float* local, float* prev, int64_t n, float weight, int wire_bf16,
+                        float server_lr, float* mom, size_t arena_off, int channel, cs_stream_t s) {
+    return fedavg_aggregate((cs_comm*)c, local, prev, n, weight, wire_bf16, server_lr, mom, arena_off, channel, 1.0f, ST(s));
+}
+int cs_fedavg_aggregate_local(cs_comm_t** group, int world, float* const* local, float* const* prev, int64_t n,
+                              const float* weights, int wire_bf16, float server_lr, float* const* mom,
+                              size_t arena_off, int channel, cs_stream_t s) {
+    return fedavg_aggregate_local((cs_comm**)group, world, local, prev, n, weights, wire_bf16, server_lr, mom,
+                                  arena_off, channel, 1.0f, ST(s));
+}
+int cs_allreduce_bucket(cs_comm_t* c, float* grad, int64_t n, float scale, int wire_bf16, size_t arena_off,
+                        int channel, cs_stream_t s) {
+    return fedavg_aggregate((cs_comm*)c, grad, nullptr, n, 1.0f, wire_bf16, 1.0f, nullptr, arena_off, channel, scale, ST(s));
+}
+int cs_allreduce_bucket_local(cs_comm_t** group, int world, float* const* grads, int64_t n, float scale,
+                              int wire_bf16, size_t arena_off, int channel, cs_stream_t s) {
+    float w[CS_MAX_RANKS];
+    for (int r = 0; r < CS_MAX_RANKS; ++r) w[r] = 1.0f;
+    return fedavg_aggregate_local((cs_comm**)group, world, grads, nullptr, n, w, wire_bf16, 1.0f, nullptr, arena_off,
+                                  channel, scale, ST(s));
+}
+
+int cs_stage_h2d(void* dst, const void* src, size_t bytes, cs_stream_t s) {
+    CS_CUDA_OK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, ST(s)));
+    return CS_OK;
+}
+int cs_stage_d2h(void* dst, const void* src, size_t bytes, cs_stream_t s) {
+    CS_CUDA_OK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, ST(s)));
+    return CS_OK;
+}
+int cs_zscore_rows(const float* x, void* y, int B, int L, int out_bf16, cs_stream_t s) {
+    return zscore_rows(x, y, B, L, out_bf16, ST(s));
+}
+
+}  // extern "C"

@@ -1,0 +1,423 @@
+// Memory-bound helper kernels: batch gather (K11), cross-entropy + loss scale (K5), flat SGD with
+// fused unscale / inf-check / scaler update (K6), z-score staging (K10), BN / ReLU / residual /
+// pooling (K4) and layout converters.  All are CUDA-core kernels sized against HBM bandwidth:
+// 128-bit accesses, grid-stride loops, one pass over the data where the math allows it.
+#include "common/cs_common.cuh"
+
+namespace cs {
+
+// ------------------------------------------------------------------------------------------------
+// K11 gather: one warp per row, 128-bit loads when L % 4 == 0
+// ------------------------------------------------------------------------------------------------
+__global__ void gather_rows_kernel(const float* __restrict__ x, const int64_t* __restrict__ y,
+                                   const int64_t* __restrict__ idx, void* __restrict__ xo,
+                                   int64_t* __restrict__ yo, int B, int L, int out_bf16) {
+    const int warps_per_block = blockDim.x >> 5;
+    const int lane = threadIdx.x & 31;
+    for (int b = blockIdx.x * warps_per_block + (threadIdx.x >> 5); b < B; b += gridDim.x * warps_per_block) {
+        const int64_t r = idx[b];
+        const float* src = x + r * (int64_t)L;
+        if (lane == 0 && yo != nullptr) yo[b] = y[r];
+        if (!out_bf16) {
+            float* dst = (float*)xo + (int64_t)b * L;
+            if ((L & 3) == 0) {
+                const float4* s4 = reinterpret_cast<const float4*>(src);
+                float4* d4 = reinterpret_cast<float4*>(dst);
+                for (int i = lane; i < (L >> 2); i += 32) d4[i] = __ldg(s4 + i);
+            } else {
+                for (int i = lane; i < L; i += 32) dst[i] = __ldg(src + i);
+            }
+        } else {
+            __nv_bfloat16* dst = (__nv_bfloat16*)xo + (int64_t)b * L;
+            for (int i = lane; i < L; i += 32) dst[i] = __float2bfloat16(__ldg(src + i));
+        }
+    }
+}
+
+int gather_rows(const float* x, const int64_t* y, const int64_t* idx, void* xo, int64_t* yo, int B,
+                int L, int out_bf16, cudaStream_t st) {
+    CS_REQUIRE(B > 0 && L > 0, "gather: bad shape B=%d L=%d", B, L);
+    int blocks = (B + 7) / 8;
+    int cap = num_sms() * 8;
+    if (blocks > cap) blocks = cap;
+    gather_rows_kernel<<<blocks, 256, 0, st>>>(x, y, idx, xo, yo, B, L, out_bf16);
+    CS_CUDA_OK(cudaGetLastError());
+    return CS_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// K5 cross entropy (mean) forward + backward with the loss scale folded into dlogits
+// ------------------------------------------------------------------------------------------------
+__global__ void ce_fwd_bwd_kernel(const float* __restrict__ logits, const int64_t* __restrict__ y,
+                                  int B, int C, const float* __restrict__ scale_ptr,
+                                  float* __restrict__ loss_out, float* __restrict__ dlogits) {
+    // single CTA; thread per sample, grid-stride over B; block reduce of the loss
+    __shared__ float red[32];
+    const float scale = scale_ptr ? *scale_ptr : 1.0f;
+    const float invB = 1.0f / (float)B;
+    float lsum = 0.0f;
+    for (int b = threadIdx.x; b < B; b += blockDim.x) {
+        const float* lg = logits + (size_t)b * C;
+        float mx = -3.0e38f;
+        for (int c = 0; c < C; ++c) mx = fmaxf(mx, lg[c]);
+        float se = 0.0f;
+        for (int c = 0; c < C; ++c) se += __expf(lg[c] - mx);
+        const float lse = mx + __logf(se);
+        const int lab = (int)y[b];
+        lsum += (lse - lg[lab]) * invB;
+        if (dlogits) {
+            for (int c = 0; c < C; ++c)
+                dlogits[(size_t)b * C + c] = (__expf(lg[c] - lse) - (c == lab ? 1.0f : 0.0f)) * invB * scale;
+        }
+    }
+    lsum = warp_sum(lsum);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = lsum;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        float v = threadIdx.x < (blockDim.x >> 5) ? red[threadIdx.x] : 0.0f;
+        v = warp_sum(v);
+        if (threadIdx.x == 0) loss_out[0] = v;
+    }
+}
+
+int cross_entropy(const float* logits, const int64_t* y, int B, int C, const float* scale_ptr,
+                  float* loss_out, float* dlogits, cudaStream_t st) {
+    CS_REQUIRE(B > 0 && C > 0 && C <= 64, "cross_entropy: bad shape B=%d C=%d", B, C);
+    int threads = B >= 1024 ? 1024 : ((B + 31) / 32) * 32;
+    ce_fwd_bwd_kernel<<<1, threads, 0, st>>>(logits, y, B, C, scale_ptr, loss_out, dlogits);
+    CS_CUDA_OK(cudaGetLastError());
+    return CS_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// K6 flat SGD-momentum, found-inf aware
+// ------------------------------------------------------------------------------------------------
+__global__ void inf_check_kernel(const float* __restrict__ g, int64_t n, int32_t* __restrict__ ctrl) {
+    int bad = 0;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+        if (!finite_f(g[i])) bad = 1;
+    bad = __syncthreads_or(bad);
+    if (bad && threadIdx.x == 0) atomicExch(ctrl + CTRL_FOUND_INF, 1);
+}
+
+__global__ void sgd_momentum_kernel(float* __restrict__ p, float* __restrict__ mom,
+                                    const float* __restrict__ g, int64_t n, float lr, float momentum,
+                                    float wd, int use_scaler, const int32_t* __restrict__ ctrl,
+                                    const float* __restrict__ fstate,
+                                    __nv_bfloat16* __restrict__ shadow) {
+    const int bad = use_scaler ? ctrl[CTRL_FOUND_INF] : 0;
+    if (bad) return;                                   // skipped step: nothing is written
+    const float inv = use_scaler ? 1.0f / fstate[FS_SCALE] : 1.0f;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    const int64_t n4 = n >> 2;
+    float4* p4 = reinterpret_cast<float4*>(p);
+    float4* m4 = reinterpret_cast<float4*>(mom);
+    const float4* g4 = reinterpret_cast<const float4*>(g);
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
+        float4 pv = p4[i], mv = m4[i], gv = g4[i];
+        mv.x = momentum * mv.x + (gv.x * inv + wd * pv.x); pv.x -= lr * mv.x;
+        mv.y = momentum * mv.y + (gv.y * inv + wd * pv.y); pv.y -= lr * mv.y;
+        mv.z = momentum * mv.z + (gv.z * inv + wd * pv.z); pv.z -= lr * mv.z;
+        mv.w = momentum * mv.w + (gv.w * inv + wd * pv.w); pv.w -= lr * mv.w;
+        p4[i] = pv; m4[i] = mv;
+        if (shadow) {
+            __nv_bfloat162* s2 = reinterpret_cast<__nv_bfloat162*>(shadow) + 2 * i;
+            s2[0] = __floats2bfloat162_rn(pv.x, pv.y);
+            s2[1] = __floats2bfloat162_rn(pv.z, pv.w);
+        }
+    }
+    for (int64_t i = (n4 << 2) + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        float pv = p[i];
+        float mv = momentum * mom[i] + (g[i] * inv + wd * pv);
+        pv -= lr * mv;
+        mom[i] = mv; p[i] = pv;
+        if (shadow) shadow[i] = __float2bfloat16(pv);
+    }
+}
+
+__global__ void scaler_update_kernel(int32_t* ctrl, float* fstate, float growth, float backoff, int interval) {
+    const int bad = ctrl[CTRL_FOUND_INF];
+    const float scale = fstate[FS_SCALE];
+    ctrl[CTRL_STEPS] += 1;
+    if (bad) { fstate[FS_SCALE] = scale * backoff; ctrl[CTRL_GROWTH] = 0; ctrl[CTRL_SKIPPED] += 1; }
+    else {
+        int t = ctrl[CTRL_GROWTH] + 1;
+        if (t >= interval) { fstate[FS_SCALE] = scale * growth; t = 0; }
+        ctrl[CTRL_GROWTH] = t;
+    }
+    ctrl[CTRL_FOUND_INF] = 0;   // cleared for the next step's inf_check (the update kernel ran before us)
+}
+
+int sgd_momentum(float* p, float* mom, const float* g, int64_t n, float lr, float momentum, float wd,
+                 int use_scaler, int32_t* ctrl, float* fstate, float growth, float backoff,
+                 int interval, void* shadow, cudaStream_t st) {
+    CS_REQUIRE(n > 0, "sgd: n must be positive");
+    CS_REQUIRE(!use_scaler || (ctrl && fstate), "sgd: scaler state missing");
+    CS_REQUIRE((((uintptr_t)p | (uintptr_t)mom | (uintptr_t)g) & 15) == 0, "sgd: buffers must be 16-byte aligned");
+    int64_t want = (n / 4 + 255) / 256;
+    int blocks = (int)(want < 1 ? 1 : (want > (int64_t)num_sms() * 8 ? (int64_t)num_sms() * 8 : want));
+    if (use_scaler) {
+        inf_check_kernel<<<blocks, 256, 0, st>>>(g, n, ctrl);
+        CS_CUDA_OK(cudaGetLastError());
+    }
+    sgd_momentum_kernel<<<blocks, 256, 0, st>>>(p, mom, g, n, lr, momentum, wd, use_scaler, ctrl, fstate,
+                                                (__nv_bfloat16*)shadow);
+    CS_CUDA_OK(cudaGetLastError());
+    if (use_scaler) {
+        scaler_update_kernel<<<1, 1, 0, st>>>(ctrl, fstate, growth, backoff, interval);
+        CS_CUDA_OK(cudaGetLastError());
+    }
+    return CS_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// K10 staging helpers
+// ------------------------------------------------------------------------------------------------
+__global__ void zscore_rows_kernel(const float* __restrict__ x, void* __restrict__ y, int B, int L, int out_bf16) {
+    const int lane = threadIdx.x & 31;
+    const int wpb = blockDim.x >> 5;
+    for (int b = blockIdx.x * wpb + (threadIdx.x >> 5); b < B; b += gridDim.x * wpb) {
+        const float* src = x + (size_t)b * L;
+        float s = 0.0f, ss = 0.0f;
+        for (int i = lane; i < L; i += 32) { float v = src[i]; s += v; ss = fmaf(v, v, ss); }
+        s = warp_sum(s); ss = warp_sum(ss);
+        const float mean = s / L;
+        const float var = fmaxf(ss / L - mean * mean, 0.0f);
+        const float inv = 1.0f / (sqrtf(var) + 1e-8f);
+        if (out_bf16) {
+            __nv_bfloat16* dst = (__nv_bfloat16*)y + (size_t)b * L;
+            for (int i = lane; i < L; i += 32) dst[i] = __float2bfloat16((src[i] - mean) * inv);
+        } else {
+            float* dst = (float*)y + (size_t)b * L;
+            for (int i = lane; i < L; i += 32) dst[i] = (src[i] - mean) * inv;
+        }
+    }
+}
+
+int zscore_rows(const float* x, void* y, int B, int L, int out_bf16, cudaStream_t st) {
+    CS_REQUIRE(B > 0 && L > 0, "zscore: bad shape");
+    int blocks = (B + 7) / 8; int cap = num_sms() * 8; if (blocks > cap) blocks = cap;
+    zscore_rows_kernel<<<blocks, 256, 0, st>>>(x, y, B, L, out_bf16);
+    CS_CUDA_OK(cudaGetLastError());
+    return CS_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// K4 BN / ReLU / residual / pool on channels-last bf16 [rows, C]
+// Thread t owns channel pair (t % (C/2)) and strides over rows -> coalesced 4-byte accesses,
+// per-thread fp32 accumulators, one atomic per (block, channel) at the end.
+// ------------------------------------------------------------------------------------------------
+__global__ void bn_stats_kernel(const __nv_bfloat162* __restrict__ x, float* __restrict__ stats, int64_t rows, int C) {
+    const int C2 = C >> 1;
+    const int cp = threadIdx.x % C2;
+    const int rlane = threadIdx.x / C2, rstep = blockDim.x / C2;
+    if (rlane >= rstep) return;
+    float s0 = 0, s1 = 0, q0 = 0, q1 = 0;
+    for (int64_t r = (int64_t)blockIdx.x * rstep + rlane; r < rows; r += (int64_t)gridDim.x * rstep) {
+        float2 v = __bfloat1622float2(x[r * C2 + cp]);
+        s0 += v.x; s1 += v.y; q0 = fmaf(v.x, v.x, q0); q1 = fmaf(v.y, v.y, q1);
+    }
+    atomicAdd(stats + 2 * cp, s0); atomicAdd(stats + 2 * cp + 1, s1);
+    atomicAdd(stats + C + 2 * cp, q0); atomicAdd(stats + C + 2 * cp + 1, q1);
+}
+
+__global__ void bn_apply_kernel(const __nv_bfloat162* __restrict__ x, const __nv_bfloat162* __restrict__ res,
+                                __nv_bfloat162* __restrict__ y, const float* __restrict__ mean,
+                                const float* __restrict__ rstd, const float* __restrict__ gamma,
+                                const float* __restrict__ beta, int64_t rows, int C, int relu) {
+    const int C2 = C >> 1;
+    const int64_t total = rows * C2;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int c = (int)(i % C2) * 2;
+        float2 v = __bfloat1622float2(x[i]);
+        float a0 = rstd[c] * gamma[c], a1 = rstd[c + 1] * gamma[c + 1];
+        float o0 = (v.x - mean[c]) * a0 + beta[c], o1 = (v.y - mean[c + 1]) * a1 + beta[c + 1];
+        if (res) { float2 r = __bfloat1622float2(res[i]); o0 += r.x; o1 += r.y; }
+        if (relu) { o0 = fmaxf(o0, 0.0f); o1 = fmaxf(o1, 0.0f); }
+        y[i] = __floats2bfloat162_rn(o0, o1);
+    }
+}
+
+__global__ void bn_bwd_reduce_kernel(const __nv_bfloat162* __restrict__ x, const __nv_bfloat162* __restrict__ y,
+                                     const __nv_bfloat162* __restrict__ dy, const float* __restrict__ mean,
+                                     const float* __restrict__ rstd, float* __restrict__ dgamma,
+                                     float* __restrict__ dbeta, int64_t rows, int C, int relu) {
+    const int C2 = C >> 1;
+    const int cp = threadIdx.x % C2;
+    const int rlane = threadIdx.x / C2, rstep = blockDim.x / C2;
+    if (rlane >= rstep) return;
+    const int c = 2 * cp;
+    const float m0 = mean[c], m1 = mean[c + 1], r0 = rstd[c], r1 = rstd[c + 1];
+    float g0 = 0, g1 = 0, b0 = 0, b1 = 0;
+    for (int64_t r = (int64_t)blockIdx.x * rstep + rlane; r < rows; r += (int64_t)gridDim.x * rstep) {
+        float2 d = __bfloat1622float2(dy[r * C2 + cp]);
+        if (relu) { float2 o = __bfloat1622float2(y[r * C2 + cp]); if (o.x <= 0.0f) d.x = 0.0f; if (o.y <= 0.0f) d.y = 0.0f; }
+        float2 v = __bfloat1622float2(x[r * C2 + cp]);
+        g0 = fmaf(d.x, (v.x - m0) * r0, g0); g1 = fmaf(d.y, (v.y - m1) * r1, g1);
+        b0 += d.x; b1 += d.y;
+    }
+    atomicAdd(dgamma + c, g0); atomicAdd(dgamma + c + 1, g1);
+    atomicAdd(dbeta + c, b0); atomicAdd(dbeta + c + 1, b1);
+}
+
+__global__ void bn_bwd_apply_kernel(const __nv_bfloat162* __restrict__ x, const __nv_bfloat162* __restrict__ y,
+                                    const __nv_bfloat162* __restrict__ dy, const float* __restrict__ mean,
+                                    const float* __restrict__ rstd, const float* __restrict__ gamma,
+                                    const float* __restrict__ dgamma, const float* __restrict__ dbeta,
+                                    __nv_bfloat162* __restrict__ dx, __nv_bfloat162* __restrict__ dres,
+                                    int64_t rows, int C, int relu) {
+    const int C2 = C >> 1;
+    const int64_t total = rows * C2;
+    const float invn = 1.0f / (float)rows;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int c = (int)(i % C2) * 2;
+        float2 d = __bfloat1622float2(dy[i]);
+        if (relu) { float2 o = __bfloat1622float2(y[i]); if (o.x <= 0.0f) d.x = 0.0f; if (o.y <= 0.0f) d.y = 0.0f; }
+        if (dres) dres[i] = __floats2bfloat162_rn(d.x, d.y);
+        float2 v = __bfloat1622float2(x[i]);
+        float xh0 = (v.x - mean[c]) * rstd[c], xh1 = (v.y - mean[c + 1]) * rstd[c + 1];
+        float o0 = gamma[c] * rstd[c] * (d.x - invn * (dbeta[c] + xh0 * dgamma[c]));
+        float o1 = gamma[c + 1] * rstd[c + 1] * (d.y - invn * (dbeta[c + 1] + xh1 * dgamma[c + 1]));
+        dx[i] = __floats2bfloat162_rn(o0, o1);
+    }
+}
+
+static int rows_grid(int64_t rows, int rstep) {
+    int64_t want = (rows + rstep - 1) / rstep;
+    int64_t cap = (int64_t)num_sms() * 4;
+    // keep >= 64 rows per thread-row so the tail atomics stay rare
+    int64_t lim = (rows + 64LL * rstep - 1) / (64LL * rstep);
+    if (want > lim) want = lim;
+    if (want > cap) want = cap;
+    return (int)(want < 1 ? 1 : want);
+}
+
+int bn_stats(const void* x, float* stats, int64_t rows, int C, cudaStream_t st) {
+    CS_REQUIRE(C >= 2 && C % 2 == 0 && C <= 2048, "bn_stats: C=%d must be even and <= 2048", C);
+    int threads = 1024; int rstep = threads / (C / 2);
+    if (rstep < 1) { threads = C / 2; rstep = 1; }
+    bn_stats_kernel<<<rows_grid(rows, rstep), threads, 0, st>>>((const __nv_bfloat162*)x, stats, rows, C);
+    CS_CUDA_OK(cudaGetLastError());
+    return CS_OK;
+}
+
+static int ew_grid(int64_t total) {
+    int64_t want = (total + 255) / 256; int64_t cap = (int64_t)num_sms() * 16;
+    return (int)(want < 1 ? 1 : (want > cap ? cap : want));
+}
+
+int bn_apply(const void* x, const void* res, void* y, const float* mean, const float* rstd,
+             const float* gamma, const float* beta, int64_t rows, int C, int relu, cudaStream_t st) {
+    CS_REQUIRE(C >= 2 && C % 2 == 0, "bn_apply: C must be even");
+    bn_apply_kernel<<<ew_grid(rows * (C / 2)), 256, 0, st>>>((const __nv_bfloat162*)x, (const __nv_bfloat162*)res,
+        (__nv_bfloat162*)y, mean, rstd, gamma, beta, rows, C, relu);
+    CS_CUDA_OK(cudaGetLastError());
+    return CS_OK;
+}
+
+int bn_bwd_reduce(const void* x, const void* y, const void* dy, const float* mean, const float* rstd,
+                  float* dgamma, float* dbeta, int64_t rows, int C, int relu, cudaStream_t st) {
+    CS_REQUIRE(C >= 2 && C % 2 == 0 && C <= 2048, "bn_bwd: C=%d must be even and <= 2048", C);
+    int threads = 1024; int rstep = threads / (C / 2);
+    if (rstep < 1) { threads = C / 2; rstep = 1; }
+    bn_bwd_reduce_kernel<<<rows_grid(rows, rstep), threads, 0, st>>>((const __nv_bfloat162*)x,
+        (const __nv_bfloat162*)y, (const __nv_bfloat162*)dy, mean, rstd, dgamma, dbeta, rows, C, relu);
+    CS_CUDA_OK(cudaGetLastError());
+    return CS_OK;
+}
+
+int bn_bwd_apply(const void* x, const void* y, const void* dy, const float* mean, const float* rstd,
+                 const float* gamma, const float* dgamma, const float* dbeta, void* dx, void* dres,
+                 int64_t rows, int C, int relu, cudaStream_t st) {
+    CS_REQUIRE(C >= 2 && C % 2 == 0, "bn_bwd: C must be even");
+    bn_bwd_apply_kernel<<<ew_grid(rows * (C / 2)), 256, 0, st>>>((const __nv_bfloat162*)x,
+        (const __nv_bfloat162*)y, (const __nv_bfloat162*)dy, mean, rstd, gamma, dgamma, dbeta,
+        (__nv_bfloat162*)dx, (__nv_bfloat162*)dres, rows, C, relu);
+    CS_CUDA_OK(cudaGetLastError());
+    return CS_OK;
+}
+
+// global average pool: block per (b, channel-pair group); threads stride over L
+__global__ void avgpool_fwd_kernel(const __nv_bfloat162* __restrict__ x, float* __restrict__ out, int B, int L, int C) {
+    const int C2 = C >> 1;
+    const int b = blockIdx.x;
+    const __nv_bfloat162* xb = x + (size_t)b * L * C2;
+    for (int cp = threadIdx.x % C2; cp < C2; cp += C2) {
+        const int rlane = threadIdx.x / C2, rstep = blockDim.x / C2;
+        float s0 = 0, s1 = 0;
+        if (rlane < rstep)
+            for (int l = rlane; l < L; l += rstep) { float2 v = __bfloat1622float2(xb[(size_t)l * C2 + cp]); s0 += v.x; s1 += v.y; }
+        if (rlane < rstep) { atomicAdd(out + (size_t)b * C + 2 * cp, s0 / L); atomicAdd(out + (size_t)b * C + 2 * cp + 1, s1 / L); }
+    }
+}
+
+__global__ void avgpool_bwd_kernel(const float* __restrict__ dout, __nv_bfloat162* __restrict__ dx, int B, int L, int C) {
+    const int C2 = C >> 1;
+    const int64_t total = (int64_t)B * L * C2;
+    const float invL = 1.0f / L;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int cp = (int)(i % C2); const int64_t b = i / ((int64_t)L * C2);
+        dx[i] = __floats2bfloat162_rn(dout[b * C + 2 * cp] * invL, dout[b * C + 2 * cp + 1] * invL);
+    }
+}
+
+int avgpool_fwd(const void* x, float* out, int B, int L, int C, cudaStream_t st) {
+    CS_REQUIRE(C % 2 == 0 && C <= 2048, "avgpool: C must be even and <= 2048");
+    CS_CUDA_OK(cudaMemsetAsync(out, 0, (size_t)B * C * sizeof(float), st));
+    int threads = C / 2 >= 1024 ? C / 2 : 1024;
+    avgpool_fwd_kernel<<<B, threads, 0, st>>>((const __nv_bfloat162*)x, out, B, L, C);
+    CS_CUDA_OK(cudaGetLastError());
+    return CS_OK;
+}
+
+int avgpool_bwd(const float* dout, void* dx, int B, int L, int C, cudaStream_t st) {
+    CS_REQUIRE(C % 2 == 0, "avgpool: C must be even");
+    avgpool_bwd_kernel<<<ew_grid((int64_t)B * L * (C / 2)), 256, 0, st>>>(dout, (__nv_bfloat162*)dx, B, L, C);
+    CS_CUDA_OK(cudaGetLastError());
+    return CS_OK;
+}
+
+// layout converters through a 32x32 smem tile transpose
+__global__ void ncl_to_nlc_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ y, int C, int L) {
+    __shared__ float tile[32][33];
+    const int b = blockIdx.z, c0 = blockIdx.y * 32, l0 = blockIdx.x * 32;
+    const float* xb = x + (size_t)b * C * L; __nv_bfloat16* yb = y + (size_t)b * C * L;
+    for (int j = threadIdx.y; j < 32; j += blockDim.y) {
+        int c = c0 + j, l = l0 + threadIdx.x;
+        tile[j][threadIdx.x] = (c < C && l < L) ? xb[(size_t)c * L + l] : 0.0f;
+    }
+    __syncthreads();
+    for (int j = threadIdx.y; j < 32; j += blockDim.y) {
+        int l = l0 + j, c = c0 + threadIdx.x;
+        if (c < C && l < L) yb[(size_t)l * C + c] = __float2bfloat16(tile[threadIdx.x][j]);
+    }
+}
+__global__ void nlc_to_ncl_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ y, int C, int L) {
+    __shared__ float tile[32][33];
+    const int b = blockIdx.z, c0 = blockIdx.y * 32, l0 = blockIdx.x * 32;
+    const __nv_bfloat16* xb = x + (size_t)b * C * L; float* yb = y + (size_t)b * C * L;
+    for (int j = threadIdx.y; j < 32; j += blockDim.y) {
+        int l = l0 + j, c = c0 + threadIdx.x;
+        tile[j][threadIdx.x] = (c < C && l < L) ? __bfloat162float(xb[(size_t)l * C + c]) : 0.0f;
+    }
+    __syncthreads();
+    for (int j = threadIdx.y; j < 32; j += blockDim.y) {
+        int c = c0 + j, l = l0 + threadIdx.x;
+        if (c < C && l < L) yb[(size_t)c * L + l] = tile[threadIdx.x][j];
+    }
+}
+int ncl_to_nlc(const float* x, void* y, int B, int C, int L, cudaStream_t st) {
+    dim3 grid((L + 31) / 32, (C + 31) / 32, B), block(32, 8);
+    ncl_to_nlc_kernel<<<grid, block, 0, st>>>(x, (__nv_bfloat16*)y, C, L);
+    CS_CUDA_OK(cudaGetLastError());
+    return CS_OK;
+}
+int nlc_to_ncl(const void* x, float* y, int B, int C, int L, cudaStream_t st) {
+    dim3 grid((L + 31) / 32, (C + 31) / 32, B), block(32, 8);
+    nlc_to_ncl_kernel<<<grid, block, 0, st>>>((const __nv_bfloat16*)x, y, C, L);
+    CS_CUDA_OK(cudaGetLastError());
+    return CS_OK;
+}
+
+}  // namespace cs

@@ -1,0 +1,265 @@
+/*
+ * crossscale.h — C ABI of the CrossScale-B200 native libraries.
+ *
+ *   libcrossscale_cuda.so   hand-written sm_100a kernels + launchers      (csrc/cuda)
+ *   libcrossscale_cpu.so    OpenMP/AVX2 CPU conv1d kernel                  (csrc/cpu)
+ *   libcrossscale_rt.so     C++ runtime: mmap shard reader, pinned ring    (csrc/runtime)
+ *
+ * Conventions: every cs_* function returns 0 on success and a non-zero code on failure;
+ * cs_last_error() then returns a message (thread local).  Pointers are device pointers unless the
+ * comment says "host".  Launchers are asynchronous on `stream` (a cudaStream_t passed as void*)
+ * and allocate nothing unless stated, so they can be captured into CUDA graphs.
+ *
+ * "ref:" comments cite the reference component (path:line under /root/reference) each entry
+ * point replaces.
+ */
+#ifndef CROSSSCALE_H_
+#define CROSSSCALE_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CS_OK 0
+#define CS_ERR_INVALID 1
+#define CS_ERR_CUDA 2
+#define CS_ERR_UNSUPPORTED 3
+
+typedef void* cs_stream_t; /* cudaStream_t */
+
+/* precision modes of the fused TinyECG kernels */
+#define CS_AMP_FP32 0 /* G0: fp32 FFMA path                                   */
+#define CS_AMP_BF16 1 /* G1: bf16 operands, fp32 accumulate (tcgen05)         */
+#define CS_AMP_FP16 2 /* G1 reference-faithful: fp16 operands + loss scaling  */
+
+const char* cs_last_error(void);
+int cs_version(void);
+/* 1 when the current device is compute capability 10.x (tcgen05 paths usable) */
+int cs_device_is_sm100(void);
+
+/* ---------------------------------------------------------------------------------------------
+ * K11  on-device batch gather.   ref: Module_3/shard_dataset.py:132-136 (x_gpu[sel], y_gpu[sel])
+ * xo[b,:] = x[idx[b],:], yo[b] = y[idx[b]].  x is [N,L] fp32; out_bf16 != 0 writes xo as bf16.
+ * ------------------------------------------------------------------------------------------- */
+int cs_gather_rows(const float* x, const int64_t* y, const int64_t* idx, void* xo, int64_t* yo,
+                   int B, int L, int out_bf16, cs_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * K6b  fused TinyECG kernels.    ref: Module_3/tiny_ecg_model.py:16-29 (model),
+ *      TRUE_FL_M3/part3_fedavg_overlap_mpi_gpu.py:103-132 (train_step_G0 / train_step_G1)
+ *
+ * `params` is the flat fp32 arena in state_dict order (1424 + 17*C floats, C <= 8).
+ * x is [rows, L]; when idx != NULL sample b reads row idx[b] (fused gather), else row b.
+ * x_bf16 != 0: x holds bf16 instead of fp32.
+ * ------------------------------------------------------------------------------------------- */
+
+/* bytes of dynamic shared memory the fused kernels need for window length L (0 if unsupported) */
+size_t cs_tiny_ecg_smem_bytes(int L, int C, int amp);
+
+/* logits[B,C] = TinyECG(x) */
+int cs_tiny_ecg_forward(const void* x, const int64_t* idx, int x_bf16, int B, int L, int C,
+                        const float* params, float* logits, int amp, cs_stream_t stream);
+
+/* grad[0:P] += dLoss/dparams given dlogits[B,C] (forward is recomputed on chip) */
+int cs_tiny_ecg_backward(const void* x, const int64_t* idx, int x_bf16, int B, int L, int C,
+                         const float* params, const float* dlogits, float* grad, int amp,
+                         cs_stream_t stream);
+
+/* One whole local training step in ONE launch: gather + forward + mean cross-entropy (x loss
+ * scale) + backward + grad unscale/inf-check + SGD-momentum update + scaler update.
+ *   y      labels, indexed like x (y[idx[b]] or y[b])
+ *   mom    momentum buffer  [P]        gacc   gradient scratch [P], must be zero on first use;
+ *                                              the kernel leaves it zero again
+ *   ctrl   int32[8]  {ticket, growth_tracker, steps_done, skipped_steps, found_inf, ...}
+ *   fstate fp32[8]   {loss_sum, loss_scale, last_loss, loss_step_scratch, ...}
+ * SGD: buf = momentum*buf + (g + wd*p); p -= lr*buf            (torch.optim.SGD, ref :181)
+ * scaler (use_scaler != 0): torch.cuda.amp.GradScaler semantics  (ref :121-127)            */
+int cs_tiny_ecg_train_step(const void* x, const int64_t* y, const int64_t* idx, int x_bf16,
+                           int B, int L, int C, float* params, float* mom, float* gacc,
+                           int32_t* ctrl, float* fstate, float lr, float momentum, float wd,
+                           int amp, int use_scaler, float growth, float backoff,
+                           int growth_interval, cs_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * K5   head-less cross entropy + loss scale, and AMP unscale / inf-check / scale update
+ *      ref: F.cross_entropy (:107,:123), GradScaler (:125-127)
+ * ------------------------------------------------------------------------------------------- */
+/* loss_out[0] = mean CE (unscaled); dlogits = scale*(softmax-onehot)/B; scale read from *scale_ptr
+ * (NULL = 1.0).  logits fp32 [B,C], C <= 64. */
+int cs_cross_entropy_fwd_bwd(const float* logits, const int64_t* y, int B, int C,
+                             const float* scale_ptr, float* loss_out, float* dlogits,
+                             cs_stream_t stream);
+
+/* K6  flat multi-tensor SGD-momentum with fused unscale + found-inf skip + scaler update.
+ * g is a flat fp32 gradient [n]; fstate/ctrl as in cs_tiny_ecg_train_step (may be NULL when
+ * use_scaler == 0).  bf16_shadow (optional) receives bf16(p) after the update.
+ * Two launches internally when use_scaler != 0 (inf-check reduce, then update).             */
+int cs_sgd_momentum(float* p, float* mom, const float* g, int64_t n, float lr, float momentum,
+                    float wd, int use_scaler, int32_t* ctrl, float* fstate, float growth,
+                    float backoff, int growth_interval, void* bf16_shadow, cs_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * K1-K3  conv1d implicit GEMM (channels-last bf16, fp32 accumulate in TMEM, TMA-fed tcgen05)
+ *        ref: nn.Conv1d -> cuDNN (tiny_ecg_model.py:17-20); CPU C13 for the microbench
+ *   x  [B, L, Cin]  bf16     w  [K, Cout, Cin] bf16 (tap-major)     y [B, Lout, Cout] bf16
+ *   stride 1 or 2, zero padding `pad`; Cin, Cout multiples of 16 (Cin<=1024, Cout<=1024).
+ *   epilogue: + bias (fp32, may be NULL), optional ReLU.
+ * ------------------------------------------------------------------------------------------- */
+int cs_conv1d_fwd(const void* x, const void* w, const float* bias, void* y, int B, int L, int Cin,
+                  int Cout, int K, int pad, int stride, int relu, cs_stream_t stream);
+/* dx = conv_transpose(dy, w):  dy [B,Lout,Cout] bf16 -> dx [B,L,Cin] bf16.  wt is the
+ * tap-flipped, channel-transposed weight [K, Cin, Cout] (cs_conv1d_prepare_dgrad_weight). */
+int cs_conv1d_dgrad(const void* dy, const void* wt, void* dx, int B, int L, int Cin, int Cout,
+                    int K, int pad, int stride, cs_stream_t stream);
+int cs_conv1d_prepare_dgrad_weight(const void* w, void* wt, int K, int Cout, int Cin,
+                                   cs_stream_t stream);
+/* dw[K,Cout,Cin] (fp32, accumulated: caller zeroes) += sum_{b,l} dy[b,l,co]*x[b,l*s+k-pad,ci];
+ * dbias[Cout] (fp32, optional) += sum dy. */
+int cs_conv1d_wgrad(const void* x, const void* dy, float* dw, float* dbias, int B, int L, int Cin,
+                    int Cout, int K, int pad, int stride, cs_stream_t stream);
+/* first layer (Cin = 1): x [B,L] fp32 -> y [B,Lout,Cout] bf16 on FFMA, + bias, optional ReLU */
+int cs_conv1d_cin1_fwd(const float* x, const float* w, const float* bias, void* y, int B, int L,
+                       int Cout, int K, int pad, int stride, int relu, cs_stream_t stream);
+int cs_conv1d_cin1_wgrad(const float* x, const void* dy, float* dw, float* dbias, int B, int L,
+                         int Cout, int K, int pad, int stride, cs_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * K4   BN / ReLU / residual / global-average-pool (channels-last bf16 activations)
+ * ------------------------------------------------------------------------------------------- */
+/* per-channel sum and sum of squares over [rows, C] -> stats[2*C] fp32 (accumulated) */
+int cs_bn_stats(const void* x, float* stats, int64_t rows, int C, cs_stream_t stream);
+/* y = relu?( (x-mean)*rstd*gamma + beta (+ residual) ); mean/rstd fp32 [C] */
+int cs_bn_apply(const void* x, const void* residual, void* y, const float* mean,
+                const float* rstd, const float* gamma, const float* beta, int64_t rows, int C,
+                int relu, cs_stream_t stream);
+/* backward of cs_bn_apply (training-mode batch statistics):
+ *   pass 1 (cs_bn_bwd_reduce): dgamma, dbeta accumulated (fp32); relu mask from y
+ *   pass 2 (cs_bn_bwd_apply):  dx (bf16), and dres = masked dy when residual was used */
+int cs_bn_bwd_reduce(const void* x, const void* y, const void* dy, const float* mean,
+                     const float* rstd, float* dgamma, float* dbeta, int64_t rows, int C, int relu,
+                     cs_stream_t stream);
+int cs_bn_bwd_apply(const void* x, const void* y, const void* dy, const float* mean,
+                    const float* rstd, const float* gamma, const float* dgamma,
+                    const float* dbeta, void* dx, void* dres, int64_t rows, int C, int relu,
+                    cs_stream_t stream);
+/* out[b,c] = mean_l x[b,l,c]  (fp32 out);   backward: dx[b,l,c] = dout[b,c]/L */
+int cs_avgpool_fwd(const void* x, float* out, int B, int L, int C, cs_stream_t stream);
+int cs_avgpool_bwd(const float* dout, void* dx, int B, int L, int C, cs_stream_t stream);
+/* fp32 [B,C,L] <-> bf16 [B,L,C] layout/precision converters */
+int cs_ncl_f32_to_nlc_bf16(const float* x, void* y, int B, int C, int L, cs_stream_t stream);
+int cs_nlc_bf16_to_ncl_f32(const void* x, float* y, int B, int C, int L, cs_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * K7-K9  in-kernel NVLink collectives over peer-mapped ("symmetric") buffers.
+ *        ref: broadcast_model / fedavg_allreduce, part3_fedavg_overlap_mpi_gpu.py:75-98
+ * No MPI / NCCL call on these paths.  A communicator is built from buffers every rank
+ * allocated identically and exchanged through CUDA IPC handles (host side, once).
+ * ------------------------------------------------------------------------------------------- */
+#define CS_MAX_RANKS 8
+#define CS_IPC_HANDLE_BYTES 64
+
+typedef struct cs_comm cs_comm_t;
+
+/* Allocate this rank's symmetric arena (`bytes`) + signal pad; writes the two IPC handles
+ * (host buffers of CS_IPC_HANDLE_BYTES each).  Allocates with cudaMalloc (not capturable). */
+int cs_comm_create(int rank, int world, size_t bytes, cs_comm_t** out, void* arena_handle_out,
+                   void* signal_handle_out);
+/* Map every peer's arena and signal pad.  `arena_handles`/`signal_handles`: host arrays of
+ * world * CS_IPC_HANDLE_BYTES gathered from all ranks (any host-side transport). */
+int cs_comm_connect(cs_comm_t* c, const void* arena_handles, const void* signal_handles);
+/* Single-process emulation for tests/1-GPU: all `world` arenas live on the current device. */
+int cs_comm_create_local(int world, size_t bytes, cs_comm_t** out /* array of `world` */);
+void* cs_comm_arena(cs_comm_t* c);          /* this rank's arena (device pointer)              */
+void* cs_comm_peer_arena(cs_comm_t* c, int r);
+size_t cs_comm_arena_bytes(cs_comm_t* c);
+int cs_comm_destroy(cs_comm_t* c);
+
+/* != 0 after a device-side barrier timed out (a peer never arrived); sticky */
+int cs_comm_status(cs_comm_t* c, int* status_out);
+
+/* K9: device-side barrier across ranks (one tiny kernel; st.release.sys / ld.acquire.sys flags in
+ * the peers' signal pads).  `channel` (0..7) selects an independent flag set so collectives on
+ * different streams do not interfere. */
+int cs_comm_barrier(cs_comm_t* c, int channel, cs_stream_t stream);
+
+/* arena bytes one aggregation of n elements needs at its offset */
+size_t cs_fedavg_arena_bytes(int64_t n, int wire_bf16, int world);
+
+/* K7: fused FedAvg.  Every rank calls it with the same n / arena_off / channel / wire format.
+ *   local      this rank's fp32 parameters [n] — read, then overwritten with the new global model
+ *   prev       global model at the start of the round [n] (updated in place), or NULL.
+ *              With prev the wire carries weight*(local-prev) (delta encoding: bf16 only quantises
+ *              the round's change) and theta <- prev + server_lr * sum_i w_i delta_i.
+ *              With prev == NULL the wire carries weight*local and theta <- sum_i w_i local_i.
+ *   weight     this client's aggregation weight n_i / sum_j n_j
+ *   wire_bf16  1: bf16 on NVLink, 0: fp32
+ *   mom        optional buffer [n] zeroed after aggregation (NULL keeps it; the reference keeps
+ *              the optimizer momentum)
+ * One-shot (n <= 65536): every rank pushes its contribution into every peer's arena, one flag
+ * round, local reduce.  Two-shot (larger): rank r reduces slice r over P2P loads and pushes the
+ * result to every peer.  Both are ONE kernel launch per rank including the cross-GPU barriers. */
+int cs_fedavg_aggregate(cs_comm_t* c, float* local, float* prev, int64_t n, float weight,
+                        int wire_bf16, float server_lr, float* mom, size_t arena_off, int channel,
+                        cs_stream_t stream);
+/* Same kernel for an emulated group (cs_comm_create_local): ONE cooperative launch covers all
+ * ranks (blockIdx.y = rank); host arrays of `world` device pointers / weights. */
+int cs_fedavg_aggregate_local(cs_comm_t** group, int world, float* const* local,
+                              float* const* prev, int64_t n, const float* weights, int wire_bf16,
+                              float server_lr, float* const* mom, size_t arena_off, int channel,
+                              cs_stream_t stream);
+
+/* K8: gradient all-reduce of one bucket, in place: grad <- scale * sum_ranks grad  (fp32 [n]).
+ * `arena_off` / `channel` let several buckets be in flight on different streams. */
+int cs_allreduce_bucket(cs_comm_t* c, float* grad, int64_t n, float scale, int wire_bf16,
+                        size_t arena_off, int channel, cs_stream_t stream);
+int cs_allreduce_bucket_local(cs_comm_t** group, int world, float* const* grads, int64_t n,
+                              float scale, int wire_bf16, size_t arena_off, int channel,
+                              cs_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * K10  pinned-host -> device staging (cudaMemcpyAsync on the given copy stream) + optional
+ *      on-device z-score normalise / fp32->bf16 repack.
+ *      ref: dead G1 code part3_mpi_gpu_train.py:222-229; LABL ring labl_loader:30-136
+ * ------------------------------------------------------------------------------------------- */
+int cs_stage_h2d(void* dst_device, const void* src_pinned_host, size_t bytes, cs_stream_t stream);
+int cs_stage_d2h(void* dst_pinned_host, const void* src_device, size_t bytes, cs_stream_t stream);
+/* y[b,:] = (x[b,:]-mean_b)/(std_b+1e-8) per window; out_bf16 selects the output type */
+int cs_zscore_rows(const float* x, void* y, int B, int L, int out_bf16, cs_stream_t stream);
+
+/* =============================================================================================
+ * libcrossscale_cpu.so
+ * C13: single-channel valid cross-correlation, batched, fp32 — same symbol and signature as the
+ * reference (Module_2/conv1d_openmp_simd.c:21-28):  y[b,i] = sum_k x[b,i+k]*w[k], outL = L-K+1
+ * ============================================================================================= */
+void conv1d_batch_omp_simd(const float* x, const float* w, float* y, int batch, int L, int K,
+                           int nthreads);
+/* which ISA path the dispatcher picked: 0 scalar, 2 AVX2+FMA, 5 AVX-512 */
+int cs_cpu_conv1d_isa(void);
+
+/* =============================================================================================
+ * libcrossscale_rt.so — LABL-style pinned ring prefetcher (C8-C10), native threads.
+ * The caller owns the slot buffers (pinned host memory, num_slots x batch x L elements).
+ * ============================================================================================= */
+typedef struct cs_prefetcher cs_prefetcher_t;
+/* out_bf16: slots hold bf16 instead of fp32.  loop != 0: restart from shard 0 at end of data.
+ * label_slots (optional, host int64 [num_slots][batch]) are filled from .lbl sidecars (0 if none). */
+cs_prefetcher_t* cs_prefetcher_create(const char* const* shard_paths, int num_shards, int batch,
+                                      int num_slots, void* const* slot_ptrs,
+                                      int64_t* const* label_slots, int normalize, int out_bf16,
+                                      int loop);
+int cs_prefetcher_window_len(cs_prefetcher_t* p);
+int cs_prefetcher_start(cs_prefetcher_t* p);
+/* Blocks until a slot is full. Returns 1 and sets slot/n_filled/fill_ms; 0 at end of data;
+ * -1 on error (message via cs_rt_last_error). */
+int cs_prefetcher_next(cs_prefetcher_t* p, int* slot, int* n_filled, double* fill_ms);
+int cs_prefetcher_recycle(cs_prefetcher_t* p, int slot);
+void cs_prefetcher_destroy(cs_prefetcher_t* p);
+const char* cs_rt_last_error(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CROSSSCALE_H_ */

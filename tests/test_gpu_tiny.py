@@ -1,0 +1,189 @@
+"""Fused TinyECG kernels and the helper kernels vs plain PyTorch fp32 oracles (needs a B200)."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def _dev():
+    return torch.device("cuda", 0)
+
+
+def _setup(C=2, B=64, L=500, seed=0):
+    from crossscale.models import TinyECG
+    torch.manual_seed(seed)
+    dev = _dev()
+    m = TinyECG(C).to(dev)
+    with torch.no_grad():                      # larger weights -> non-degenerate ReLU masks and logits
+        for p in m.parameters():
+            p.mul_(2.0)
+    x = torch.randn(B, 1, L, device=dev)
+    y = torch.randint(0, C, (B,), device=dev)
+    return m, x, y
+
+
+def _oracle_grads(m, x, y, scale=1.0):
+    m.zero_grad(set_to_none=True)
+    for p in m.parameters():
+        p.grad = None
+    loss = F.cross_entropy(m.forward_reference(x), y)
+    (loss * scale).backward()
+    g = torch.cat([p.grad.reshape(-1) for p in m.parameters()])
+    return float(loss), g
+
+
+@pytest.mark.parametrize("C,B,L", [(2, 64, 500), (5, 37, 360), (2, 300, 500), (8, 5, 97)])
+def test_fused_forward_fp32(C, B, L):
+    from crossscale.ops import tiny_ecg as tk
+    m, x, y = _setup(C, B, L)
+    with torch.no_grad():
+        ref = m.forward_reference(x)
+    flat = m.flatten_parameters()
+    out = tk.forward_logits(x, flat.flat, C, tk.AMP_FP32)
+    torch.testing.assert_close(out, ref, rtol=1e-4, atol=1e-4)
+
+
+@pytest.mark.parametrize("C,B,L", [(2, 64, 500), (5, 37, 360), (2, 300, 500)])
+def test_fused_backward_fp32(C, B, L):
+    from crossscale.ops import tiny_ecg as tk
+    m, x, y = _setup(C, B, L)
+    flat = m.flatten_parameters()
+    params = flat.flat.clone()
+    _, g_ref = _oracle_grads(m, x, y)
+    with torch.no_grad():
+        logits = m.forward_reference(x)
+        dlog = (torch.softmax(logits, 1) - F.one_hot(y, C).float()) / B
+    g = tk.backward_grads(x, params, dlog, C, tk.AMP_FP32)
+    torch.testing.assert_close(g[: g_ref.numel()], g_ref, rtol=2e-3, atol=2e-5)
+
+
+def test_autograd_bridge_matches_reference():
+    m, x, y = _setup(5, 48, 360)
+    _, g_ref = _oracle_grads(m, x, y)
+    for p in m.parameters():
+        p.grad = None
+    m.flatten_parameters()
+    loss = F.cross_entropy(m(x), y)             # CUDA path: fused forward kernel
+    loss.backward()                              # fused backward kernel
+    g = m.flatten_parameters().flat.grad if m.flatten_parameters().flat.grad is not None else None
+    got = torch.cat([p.grad.reshape(-1) for p in m.parameters()]) if g is None else g[: g_ref.numel()]
+    torch.testing.assert_close(got, g_ref, rtol=2e-3, atol=2e-5)
+
+
+@pytest.mark.parametrize("amp_name", ["none", "bf16", "fp16"])
+def test_fused_train_step_tracks_torch_sgd(amp_name):
+    from crossscale.models import TinyECG
+    from crossscale.ops import tiny_ecg as tk
+    C, B, L, steps = 2, 128, 500, 5
+    m, x, y = _setup(C, B, L, seed=3)
+    ref = TinyECG(C).to(_dev())
+    ref.load_state_dict(m.state_dict())
+    opt = torch.optim.SGD(ref.parameters(), lr=1e-2, momentum=0.9)
+    flat = m.flatten_parameters()
+    amp = tk.AMP_BY_NAME[amp_name]
+    st = tk.TinyTrainState(flat.flat, C, lr=1e-2, momentum=0.9, amp=amp,
+                           scaler=tk.ScalerConfig(enabled=(amp_name == "fp16")))
+    losses = []
+    for s in range(steps):
+        xb = torch.randn(B, 1, L, device=_dev(), generator=None)
+        yb = torch.randint(0, C, (B,), device=_dev())
+        opt.zero_grad(set_to_none=True)
+        l = F.cross_entropy(ref.forward_reference(xb), yb)
+        l.backward()
+        opt.step()
+        losses.append(float(l))
+        st.step(xb, yb)
+    torch.cuda.synchronize()
+    tol = dict(rtol=1e-3, atol=1e-5) if amp_name == "none" else dict(rtol=5e-2, atol=2e-3)
+    got = flat.flat[: tk.MAX_CLASSES * 0 + 1424 + 17 * C]
+    want = torch.cat([p.detach().reshape(-1) for p in ref.parameters()])
+    torch.testing.assert_close(got, want, **tol)
+    assert abs(st.loss_sum() - sum(losses)) < (1e-3 if amp_name == "none" else 5e-2) * steps
+    assert st.steps_done() == steps and st.skipped_steps() == 0
+    assert float(st.gacc.abs().max()) == 0.0     # scratch left zero for the next step
+    if amp_name == "fp16":
+        assert st.loss_scale() == 65536.0
+
+
+def test_scaler_skips_step_on_inf_and_backs_off():
+    from crossscale.ops import tiny_ecg as tk
+    m, x, y = _setup(2, 32, 500)
+    flat = m.flatten_parameters()
+    st = tk.TinyTrainState(flat.flat, 2, amp=tk.AMP_FP32, scaler=tk.ScalerConfig(enabled=True, growth_interval=2))
+    before = flat.flat.clone()
+    xbad = x.clone()
+    xbad[0, 0, 10] = float("inf")
+    st.step(xbad, y)
+    torch.cuda.synchronize()
+    torch.testing.assert_close(flat.flat, before)                # parameters untouched
+    assert st.skipped_steps() == 1 and st.loss_scale() == 32768.0
+    assert float(st.mom.abs().max()) == 0.0 and float(st.gacc.abs().max()) == 0.0
+    st.step(x, y); st.step(x, y)
+    torch.cuda.synchronize()
+    assert st.loss_scale() == 65536.0 and st.steps_done() == 3   # grew after 2 clean steps
+    assert not torch.equal(flat.flat, before)
+
+
+def test_fused_gather_index_path_equals_materialised_batch():
+    from crossscale.ops import tiny_ecg as tk
+    from crossscale.ops.gather import gather_rows
+    m, _, _ = _setup(2, 8, 500)
+    data = torch.randn(1000, 500, device=_dev())
+    labels = torch.randint(0, 2, (1000,), device=_dev())
+    idx = torch.randperm(1000, device=_dev())[:96]
+    xb, yb = gather_rows(data, labels, idx)
+    torch.testing.assert_close(xb, data[idx]); assert torch.equal(yb, labels[idx])
+    xh, _ = gather_rows(data, None, idx, out_bf16=True)
+    torch.testing.assert_close(xh.float(), data[idx].bfloat16().float())
+    flat = m.flatten_parameters()
+    a = tk.forward_logits(data, flat.flat, 2, tk.AMP_FP32, idx=idx)
+    b = tk.forward_logits(xb, flat.flat, 2, tk.AMP_FP32)
+    torch.testing.assert_close(a, b, rtol=0, atol=0)
+    s1 = tk.TinyTrainState(flat.flat.clone(), 2)
+    s2 = tk.TinyTrainState(flat.flat.clone(), 2)
+    s1.step(data, labels, idx=idx); s2.step(xb, yb)
+    torch.cuda.synchronize()
+    torch.testing.assert_close(s1.params, s2.params, rtol=1e-5, atol=1e-7)
+
+
+def test_cross_entropy_and_sgd_kernels():
+    import ctypes as C
+    from crossscale.ops import _lib
+    lib, dev = _lib.cuda_lib(), _dev()
+    torch.manual_seed(0)
+    logits = torch.randn(500, 5, device=dev) * 3
+    y = torch.randint(0, 5, (500,), device=dev)
+    scale = torch.tensor([128.0], device=dev)
+    loss = torch.zeros(1, device=dev); dl = torch.empty_like(logits)
+    _lib.check(lib.cs_cross_entropy_fwd_bwd(logits.data_ptr(), y.data_ptr(), 500, 5, scale.data_ptr(),
+                                            loss.data_ptr(), dl.data_ptr(), _lib.stream_ptr()))
+    lg = logits.clone().requires_grad_(True)
+    ref = F.cross_entropy(lg, y); (ref * 128.0).backward()
+    torch.testing.assert_close(loss[0], ref.detach(), rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(dl, lg.grad, rtol=1e-4, atol=1e-6)
+    # SGD with scaler: clean step then inf step
+    n = 100003
+    p = torch.randn(n + 1, device=dev)[:n]; p = torch.randn(n, device=dev)
+    p0 = p.clone(); mom = torch.zeros(n, device=dev); g = torch.randn(n, device=dev) * 64.0
+    ctrl = torch.zeros(8, dtype=torch.int32, device=dev); fs = torch.zeros(8, device=dev); fs[1] = 64.0
+    sh = torch.empty(n, dtype=torch.bfloat16, device=dev)
+    args = lambda: (p.data_ptr(), mom.data_ptr(), g.data_ptr(), n, 0.01, 0.9, 0.0, 1, ctrl.data_ptr(), fs.data_ptr(),
+                    2.0, 0.5, 2000, sh.data_ptr(), _lib.stream_ptr())
+    _lib.check(lib.cs_sgd_momentum(*args()))
+    torch.testing.assert_close(p, p0 - 0.01 * (g / 64.0), rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(sh.float(), p.bfloat16().float())
+    g[17] = float("nan"); p1 = p.clone()
+    _lib.check(lib.cs_sgd_momentum(*args()))
+    torch.cuda.synchronize()
+    torch.testing.assert_close(p, p1)
+    assert float(fs[1]) == 32.0 and int(ctrl[3]) == 1 and int(ctrl[2]) == 2
+
+
+def test_zscore_kernel():
+    from crossscale.ops import _lib
+    x = torch.randn(300, 360, device=_dev()) * 3 + 1
+    out = torch.empty_like(x)
+    _lib.check(_lib.cuda_lib().cs_zscore_rows(x.data_ptr(), out.data_ptr(), 300, 360, 0, _lib.stream_ptr()))
+    ref = (x - x.mean(1, keepdim=True)) / (x.std(1, unbiased=False, keepdim=True) + 1e-8)
+    torch.testing.assert_close(out, ref, rtol=1e-4, atol=1e-4)
