@@ -122,7 +122,7 @@ class TinyECG(nn.Module):
             from ..ops import tiny_ecg as _k
             if _k.use_kernels():
                 flat = self.flatten_parameters()
-                return _k.TinyECGLogits.apply(x, flat.flat, self.num_classes, flat.numel)
+                return _k.TinyECGLogits.apply(x, flat.flat, self.num_classes, *flat.params)
         return self.forward_reference(x)
 
 

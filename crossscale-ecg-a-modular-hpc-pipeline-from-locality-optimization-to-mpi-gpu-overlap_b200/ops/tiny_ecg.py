@@ -60,21 +60,32 @@ def backward_grads(x: torch.Tensor, params: torch.Tensor, dlogits: torch.Tensor,
 
 
 class TinyECGLogits(torch.autograd.Function):
-    """autograd bridge: logits = TinyECG(x; flat params); backward recomputes activations on chip."""
+    """autograd bridge: ``logits = TinyECG(x; params)``; backward recomputes activations on chip.
+
+    ``flat`` is the arena the kernels read; ``params`` are the six ``nn.Parameter`` views of it, passed
+    so that autograd routes the flat gradient back to them.
+    """
 
     @staticmethod
-    def forward(ctx, x, flat, num_classes, numel):
+    def forward(ctx, x, flat, num_classes, *params):
         amp = AMP_BF16 if torch.is_autocast_enabled() else AMP_FP32
         ctx.save_for_backward(x, flat)
-        ctx.meta = (num_classes, numel, amp)
+        ctx.meta = (num_classes, amp, [p.shape for p in params])
         return forward_logits(x, flat, num_classes, amp)
 
     @staticmethod
     def backward(ctx, dlogits):
         x, flat = ctx.saved_tensors
-        num_classes, numel, amp = ctx.meta
+        num_classes, amp, shapes = ctx.meta
         g = backward_grads(x, flat, dlogits.float(), num_classes, amp)
-        return None, g, None, None
+        outs, off = [], 0
+        for shp in shapes:
+            n = 1
+            for d in shp:
+                n *= d
+            outs.append(g[off:off + n].view(shp))
+            off += n
+        return (None, None, None, *outs)
 
 
 @dataclass

@@ -1,4 +1,4 @@
-// temporary stubs (replaced by conv1d_umma.cu / tiny_ecg_umma.cu)
+// temporary stubs (replaced by conv1d_umma.cu)
 #include "tiny_ecg.cuh"
 namespace cs {
 #define UNSUP(name) set_error(name ": not built yet"); return CS_ERR_UNSUPPORTED
@@ -7,9 +7,4 @@ int conv1d_prepare_dgrad_weight(const void*, void*, int, int, int, cudaStream_t)
 int conv1d_wgrad(const void*, const void*, float*, float*, int, int, int, int, int, int, int, cudaStream_t) { UNSUP("wgrad"); }
 int conv1d_cin1_fwd(const float*, const float*, const float*, void*, int, int, int, int, int, int, int, cudaStream_t) { UNSUP("cin1_fwd"); }
 int conv1d_cin1_wgrad(const float*, const void*, float*, float*, int, int, int, int, int, int, cudaStream_t) { UNSUP("cin1_wgrad"); }
-int tiny_umma_forward(const TinyArgs&, cudaStream_t) { UNSUP("tiny_umma"); }
-int tiny_umma_backward(const TinyArgs&, cudaStream_t) { UNSUP("tiny_umma"); }
-int tiny_umma_train(const TinyArgs&, cudaStream_t) { UNSUP("tiny_umma"); }
-size_t tiny_umma_smem_bytes(int, int) { return 0; }
-bool tiny_umma_supported(int, int) { return false; }
 }

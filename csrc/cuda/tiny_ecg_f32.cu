@@ -288,30 +288,33 @@ __global__ void __launch_bounds__(kThreads, 2) tiny_ecg_f32_kernel(TinyArgs a) {
     }
 }
 
-static int launch_f32(int mode, const TinyArgs& a, cudaStream_t st) {
+template <int MODE>
+static int launch_f32_mode(const TinyArgs& a, cudaStream_t st) {
     CS_REQUIRE(a.C >= 1 && a.C <= kMaxC, "TinyECG fused kernels support 1..%d classes (got %d)", kMaxC, a.C);
     CS_REQUIRE(a.B >= 1 && a.L >= 8, "bad shape B=%d L=%d", a.B, a.L);
     SmemPlan sp(a.L, a.C);
-    size_t smem = (size_t)sp.total * sizeof(float);
-    CS_REQUIRE(smem <= 227 * 1024, "window length %d needs %zu B smem (> 227 KB)", a.L, smem);
-    int per_sm = smem <= 113 * 1024 ? 2 : 1;
-    int grid = a.B < num_sms() * per_sm ? a.B : num_sms() * per_sm;
-    auto go = [&](auto kern) -> int {
-        // opt in to >48 KB dynamic smem once per device, outside any stream capture
-        static bool done[64] = {};
-        int dev = 0;
-        CS_CUDA_OK(cudaGetDevice(&dev));
-        if (!done[dev & 63]) {
-            CS_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-            done[dev & 63] = true;
-        }
-        kern<<<grid, kThreads, smem, st>>>(a);
-        CS_CUDA_OK(cudaGetLastError());
-        return CS_OK;
-    };
-    if (mode == MODE_FWD) return go(tiny_ecg_f32_kernel<MODE_FWD>);
-    if (mode == MODE_BWD) return go(tiny_ecg_f32_kernel<MODE_BWD>);
-    return go(tiny_ecg_f32_kernel<MODE_TRAIN>);
+    const size_t smem = (size_t)sp.total * sizeof(float);
+    CS_REQUIRE(smem <= 225 * 1024, "window length %d needs %zu B smem (> 225 KB)", a.L, smem);
+    const int per_sm = smem <= 110 * 1024 ? 2 : 1;
+    const int grid = a.B < num_sms() * per_sm ? a.B : num_sms() * per_sm;
+    // opt in to >48 KB dynamic smem; raised only when a longer window needs more (never in the steady
+    // state, so CUDA-graph capture sees no attribute calls).  One record per kernel instantiation.
+    static size_t configured[64] = {};
+    int dev = 0;
+    CS_CUDA_OK(cudaGetDevice(&dev));
+    if (smem > configured[dev & 63]) {
+        CS_CUDA_OK(cudaFuncSetAttribute(tiny_ecg_f32_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured[dev & 63] = smem;
+    }
+    tiny_ecg_f32_kernel<MODE><<<grid, kThreads, smem, st>>>(a);
+    CS_CUDA_OK(cudaGetLastError());
+    return CS_OK;
+}
+
+static int launch_f32(int mode, const TinyArgs& a, cudaStream_t st) {
+    if (mode == MODE_FWD) return launch_f32_mode<MODE_FWD>(a, st);
+    if (mode == MODE_BWD) return launch_f32_mode<MODE_BWD>(a, st);
+    return launch_f32_mode<MODE_TRAIN>(a, st);
 }
 
 int tiny_f32_forward(const TinyArgs& a, cudaStream_t st) { return launch_f32(MODE_FWD, a, st); }

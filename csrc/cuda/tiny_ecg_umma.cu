@@ -1,0 +1,493 @@
+// Fused TinyECG kernels, tcgen05 / TMEM path (config G1: bf16 or fp16 operands, fp32 accumulate).
+//
+// One CTA (128 threads = the 128 TMEM lanes) walks its samples; every activation of a sample lives
+// in shared memory in the *no-swizzle UMMA core-matrix layout*, written there directly by the
+// producing CUDA-core code, so the tensor core consumes it without any repacking:
+//
+//   plane p of a [rows, 16ch] activation = rows x 8 channels, 16 bytes per row, rows contiguous.
+//   * as a K-major A operand (rows = M = positions, channels = K): SBO = 128 B (8-row group),
+//     LBO = plane stride.  A conv tap is a descriptor whose start address is shifted by
+//     tap*16 bytes — the activation is stored ONCE, no im2col, no per-tap copies.
+//   * as an MN-major operand (rows = K = positions, channels = M or N): LBO = 128 B,
+//     SBO = plane stride — or SBO = 16 B, which makes M-group g the SAME plane shifted by g rows,
+//     i.e. one MMA produces the weight gradient of 8 channels x up to 16 taps at once.
+//
+//   conv2 fwd   D[l, co]      = sum_k  h1[l+k-2, :] . W2[co, :, k]        5 MMAs / 128 positions
+//   conv2 dgrad D[l, ci]      = sum_k dz2[l-k+2, :] . W2[:, ci, k]        5 MMAs / 128 positions
+//   conv2 wgrad D[(k,c8), co] = sum_l  h1[l+k-2, 8j+c8] * dz2[l, co]      2 MMAs / 16 positions
+//   conv1 wgrad + both bias grads D[k, n] = sum_l xcol[l, k] * [dz1 | dz2][l, n]   (xcol = im2col of
+//               x with a ones column: 7 taps + bias)                        1 MMA  / 16 positions
+//
+// Weight-gradient accumulators stay in TMEM across all samples of the CTA and are read out once.
+// conv1 forward (Cin = 1, reduction 7) does not fit the tensor core and runs on FFMA, writing bf16
+// straight into the operand planes.  MODE_TRAIN ends with the last-CTA SGD/scaler tail, so a local
+// step is ONE launch (ref: train_step_G1, TRUE_FL_M3/part3_fedavg_overlap_mpi_gpu.py:117-132).
+#include "tiny_ecg.cuh"
+#include "common/tcgen05.cuh"
+
+namespace cs {
+
+using namespace tc;
+
+constexpr int kUThreads = 128;
+#ifndef CS_TINY_WGRAD_M
+#define CS_TINY_WGRAD_M 128      // M of the weight-gradient MMAs (128: row r -> TMEM lane r)
+#endif
+
+template <int TILES> struct USmem {
+    static constexpr int ROWS = TILES * 128 + 16;          // 8 halo rows on top, >= 8 below
+    static constexpr int PLANE = ROWS * 16;                // bytes
+    static constexpr int OFF_BAR = 0;                      // 3 mbarriers, tmem slot, flags
+    static constexpr int OFF_F32 = 64;                     // fp32 scalars (see F32_* below)
+    static constexpr int F32_COUNT = 112 + 16 + 16 + 128 + 8 + 16 + 8 + 16 + 64;
+    static constexpr int OFF_WT = (OFF_F32 + F32_COUNT * 4 + 127) & ~127;   // 10 weight tiles x 512 B
+    static constexpr int OFF_XS = OFF_WT + 10 * 512;
+    static constexpr int XS_LEN = TILES * 128 + 8;
+    static constexpr int OFF_PLANES = (OFF_XS + XS_LEN * 4 + 127) & ~127;
+    // plane order matters: [dz1 p0][dz1 p1][dz2 p0][dz2 p1] are the 4 N-groups of the bias MMA
+    static constexpr int P_DZ1 = OFF_PLANES, P_DZ2 = P_DZ1 + 2 * PLANE, P_H1 = P_DZ2 + 2 * PLANE,
+                         P_XCOL = P_H1 + 2 * PLANE;
+    static constexpr int TOTAL = P_XCOL + PLANE + 512;     // slack: shifted operands read past the end
+    static constexpr int TMEM_COLS = (16 * TILES + 64) <= 128 ? 128 : 256;
+};
+
+template <bool FP16> __device__ __forceinline__ uint32_t pack2(float a, float b) {
+    if (FP16) { __half2 h = __floats2half2_rn(a, b); return *reinterpret_cast<uint32_t*>(&h); }
+    __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<uint32_t*>(&h);
+}
+template <bool FP16> __device__ __forceinline__ float round_half(float a) {
+    return FP16 ? __half2float(__float2half_rn(a)) : __bfloat162float(__float2bfloat16(a));
+}
+template <bool FP16> __device__ __forceinline__ float2 unpack2(uint32_t u) {
+    if (FP16) return __half22float2(*reinterpret_cast<__half2*>(&u));
+    return __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&u));
+}
+template <bool FP16> __device__ __forceinline__ uint16_t pack1(float a) {
+    if (FP16) { __half h = __float2half_rn(a); return *reinterpret_cast<uint16_t*>(&h); }
+    __nv_bfloat16 h = __float2bfloat16(a);
+    return *reinterpret_cast<uint16_t*>(&h);
+}
+
+// 16 per-lane partial sums -> lane j ends with the warp total of channel (j >> 1)
+__device__ __forceinline__ float warp_reduce16(const float (&p)[16], int lane) {
+    float a8[8], a4[4], a2[2];
+    const bool h16 = lane & 16, h8 = lane & 8, h4 = lane & 4, h2 = lane & 2;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        const float send = h16 ? p[j] : p[j + 8], keep = h16 ? p[j + 8] : p[j];
+        a8[j] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const float send = h8 ? a8[j] : a8[j + 4], keep = h8 ? a8[j + 4] : a8[j];
+        a4[j] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+    }
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+        const float send = h4 ? a4[j] : a4[j + 2], keep = h4 ? a4[j + 2] : a4[j];
+        a2[j] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+    }
+    const float send = h2 ? a2[0] : a2[1], keep = h2 ? a2[1] : a2[0];
+    float v = keep + __shfl_xor_sync(0xffffffffu, send, 2);
+    v += __shfl_xor_sync(0xffffffffu, v, 1);
+    return v;
+}
+
+template <int TILES, bool FP16, int MODE>
+__global__ void __launch_bounds__(kUThreads) tiny_umma_kernel(TinyArgs a) {
+    using S = USmem<TILES>;
+    extern __shared__ __align__(128) uint8_t smem[];
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const int L = a.L, C = a.C;
+    const int tiles = (L + 127) >> 7;
+
+    uint64_t* bar_fwd = reinterpret_cast<uint64_t*>(smem + S::OFF_BAR);
+    uint64_t* bar_dg = bar_fwd + 1;
+    uint64_t* bar_wg = bar_fwd + 2;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + S::OFF_BAR + 24);
+    int* is_last = reinterpret_cast<int*>(smem + S::OFF_BAR + 28);
+    float* f32 = reinterpret_cast<float*>(smem + S::OFF_F32);
+    float* w1s = f32;            float* b1s = w1s + 112;   float* b2s = b1s + 16;   float* whs = b2s + 16;
+    float* bhs = whs + 128;      float* pooled = bhs + 8;  float* dlog = pooled + 16; float* gj = dlog + 8;
+    float* red = gj + 16;
+    uint8_t* wt = smem + S::OFF_WT;
+    float* xs = reinterpret_cast<float*>(smem + S::OFF_XS);
+    const float* prm = a.params;
+
+    // ---- one-time set-up ------------------------------------------------------------------------
+    {   // zero every operand plane + xs: halo rows / tail rows / slack stay zero (and finite) forever
+        uint4* z = reinterpret_cast<uint4*>(smem + S::OFF_XS);
+        const int n16 = (S::TOTAL - S::OFF_XS) / 16;
+        for (int i = t; i < n16; i += kUThreads) z[i] = make_uint4(0, 0, 0, 0);
+    }
+    for (int i = t; i < 112; i += kUThreads) w1s[i] = prm[TinyLayout::W1 + i];
+    if (t < 16) { b1s[t] = prm[TinyLayout::B1 + t]; b2s[t] = prm[TinyLayout::B2 + t]; }
+    for (int i = t; i < 16 * C; i += kUThreads) whs[i] = prm[TinyLayout::WH + i];
+    if (t < C) bhs[t] = prm[TinyLayout::bh(C) + t];
+    for (int i = t; i < 1280; i += kUThreads) {        // W2 [co][ci][k] -> K-major 16x16 tiles per tap
+        const int co = i / 80, ci = (i / 5) & 15, k = i % 5;
+        const uint16_t h = pack1<FP16>(prm[TinyLayout::W2 + i]);
+        // forward tile k:  B[n = co][kk = ci];  dgrad tile 5+k:  B[n = ci][kk = co]
+        const int off_f = (co & 7) * 16 + (co >> 3) * 128 + (ci >> 3) * 256 + (ci & 7) * 2;
+        const int off_d = (ci & 7) * 16 + (ci >> 3) * 128 + (co >> 3) * 256 + (co & 7) * 2;
+        *reinterpret_cast<uint16_t*>(wt + k * 512 + off_f) = h;
+        if (MODE != MODE_FWD) *reinterpret_cast<uint16_t*>(wt + (5 + k) * 512 + off_d) = h;
+    }
+    if (t == 0) {
+        mbar_init(bar_fwd, 1); mbar_init(bar_dg, 1); mbar_init(bar_wg, 1);
+        fence_mbar_init();
+    }
+    if (warp == 0) tmem_alloc(tmem_slot, S::TMEM_COLS);
+    fence_proxy_async_smem();
+    tc_fence_before_sync();
+    __syncthreads();
+    tc_fence_after_sync();
+    const uint32_t tmem_base = *tmem_slot;
+    const uint32_t tmem_lane = tmem_base + ((uint32_t)(warp * 32) << 16);
+    const uint32_t col_w = 16 * TILES, col_b = 16 * TILES + 32;
+
+    const uint32_t s_base = smem_u32(smem);
+    const uint32_t s_dz1 = s_base + S::P_DZ1, s_dz2 = s_base + S::P_DZ2, s_h1 = s_base + S::P_H1,
+                   s_xcol = s_base + S::P_XCOL, s_wt = s_base + S::OFF_WT;
+    constexpr uint32_t FMT = FP16 ? FMT_F16 : FMT_BF16;
+    constexpr uint32_t ID_CONV = idesc_f16(FMT, 128, 16, MAJOR_K, MAJOR_K);
+    constexpr uint32_t ID_WG = idesc_f16(FMT, CS_TINY_WGRAD_M, 16, MAJOR_MN, MAJOR_MN);
+    constexpr uint32_t ID_WB = idesc_f16(FMT, CS_TINY_WGRAD_M, 32, MAJOR_MN, MAJOR_MN);
+
+    const float invL = 1.0f / (float)L, invB = 1.0f / (float)a.B;
+    const float lscale = (MODE == MODE_TRAIN && a.use_scaler) ? a.fstate[FS_SCALE] : 1.0f;
+    float ghead0 = 0.0f, ghead1 = 0.0f, loss_acc = 0.0f;
+    uint32_t it = 0;
+
+    for (int s = blockIdx.x; s < a.B; s += gridDim.x, ++it) {
+        const uint32_t par = it & 1;
+        const int64_t row = a.idx ? a.idx[s] : (int64_t)s;
+        // ---- P1: window -> xs (rounded to the operand type, as autocast would feed conv1) --------
+        float xin[TILES];
+#pragma unroll
+        for (int i = 0; i < TILES; ++i) {
+            const int l = i * 128 + t;
+            float v = 0.0f;
+            if (l < L) v = a.x_bf16 ? __bfloat162float(((const __nv_bfloat16*)a.x)[row * L + l])
+                                    : __ldg((const float*)a.x + row * L + l);
+            xin[i] = round_half<FP16>(v);
+        }
+        int label = 0;
+        if (MODE == MODE_TRAIN && t == 0) label = (int)a.y[row];
+        if (MODE != MODE_FWD && it > 0) mbar_wait(bar_wg, par ^ 1);   // previous sample's MMAs released the planes
+#pragma unroll
+        for (int i = 0; i < TILES; ++i) { const int l = i * 128 + t; if (l < L) xs[l + 3] = xin[i]; }
+        __syncthreads();
+
+        // ---- P2: conv1 + ReLU on FFMA -> h1 planes; im2col(x)+ones -> xcol plane ------------------
+        {
+            float xv[TILES][7];
+#pragma unroll
+            for (int i = 0; i < TILES; ++i)
+#pragma unroll
+                for (int k = 0; k < 7; ++k) xv[i][k] = xs[i * 128 + t + k];
+            uint32_t hp[TILES][8];
+#pragma unroll
+            for (int c = 0; c < 16; c += 2) {
+                float w0[7], w1[7];
+#pragma unroll
+                for (int k = 0; k < 7; ++k) { w0[k] = w1s[c * 7 + k]; w1[k] = w1s[(c + 1) * 7 + k]; }
+                const float bb0 = b1s[c], bb1 = b1s[c + 1];
+#pragma unroll
+                for (int i = 0; i < TILES; ++i) {
+                    float a0 = bb0, a1 = bb1;
+#pragma unroll
+                    for (int k = 0; k < 7; ++k) { a0 = fmaf(w0[k], xv[i][k], a0); a1 = fmaf(w1[k], xv[i][k], a1); }
+                    hp[i][c >> 1] = pack2<FP16>(fmaxf(a0, 0.0f), fmaxf(a1, 0.0f));
+                }
+            }
+#pragma unroll
+            for (int i = 0; i < TILES; ++i) {
+                const int l = i * 128 + t;
+                if (l < L) {
+                    const int ro = (l + 8) * 16;
+                    *reinterpret_cast<uint4*>(smem + S::P_H1 + ro) = make_uint4(hp[i][0], hp[i][1], hp[i][2], hp[i][3]);
+                    *reinterpret_cast<uint4*>(smem + S::P_H1 + S::PLANE + ro) = make_uint4(hp[i][4], hp[i][5], hp[i][6], hp[i][7]);
+                    if (MODE != MODE_FWD)
+                        *reinterpret_cast<uint4*>(smem + S::P_XCOL + ro) =
+                            make_uint4(pack2<FP16>(xv[i][0], xv[i][1]), pack2<FP16>(xv[i][2], xv[i][3]),
+                                       pack2<FP16>(xv[i][4], xv[i][5]), pack2<FP16>(xv[i][6], 1.0f));
+                }
+            }
+        }
+        fence_proxy_async_smem();
+        tc_fence_before_sync();
+        __syncthreads();
+
+        // ---- conv2 forward on the tensor core ---------------------------------------------------------
+        if (t == 0) {
+            tc_fence_after_sync();
+            for (int i = 0; i < tiles; ++i)
+#pragma unroll
+                for (int k = 0; k < 5; ++k)
+                    mma_f16(tmem_base + i * 16, smem_desc(s_h1 + (i * 128 + 6 + k) * 16, S::PLANE, 128),
+                            smem_desc(s_wt + k * 512, 256, 128), ID_CONV, k > 0);
+            mma_commit(bar_fwd);
+        }
+        mbar_wait(bar_fwd, par);
+        tc_fence_after_sync();
+
+        // ---- epilogue 1: bias + ReLU + pool partials, ReLU mask kept in registers --------------------
+        float pool[16];
+#pragma unroll
+        for (int c = 0; c < 16; ++c) pool[c] = 0.0f;
+        uint32_t mask[TILES];
+#pragma unroll
+        for (int i = 0; i < TILES; ++i) {
+            mask[i] = 0;
+            if (i < tiles) {
+                uint32_t v[16];
+                tmem_ld16(tmem_lane + i * 16, v);
+                tmem_ld_wait();
+                const bool valid = (i * 128 + t) < L;
+#pragma unroll
+                for (int c = 0; c < 16; ++c) {
+                    const float z = __uint_as_float(v[c]) + b2s[c];
+                    if (valid && z > 0.0f) { pool[c] += z; mask[i] |= 1u << c; }
+                }
+            }
+        }
+        {
+            const float v = warp_reduce16(pool, lane);
+            if ((lane & 1) == 0) red[warp * 16 + (lane >> 1)] = v;
+        }
+        tc_fence_before_sync();
+        __syncthreads();
+        if (t < 16) pooled[t] = (red[t] + red[16 + t] + red[32 + t] + red[48 + t]) * invL;
+        __syncthreads();
+
+        // ---- head + cross entropy ------------------------------------------------------------------------
+        if (t == 0) {
+            float lg[kTinyMaxC];
+            float mx = -3.0e38f;
+            for (int c = 0; c < C; ++c) {
+                float v = bhs[c];
+#pragma unroll
+                for (int j = 0; j < 16; ++j) v = fmaf(whs[c * 16 + j], pooled[j], v);
+                lg[c] = v; mx = fmaxf(mx, v);
+            }
+            if (MODE == MODE_FWD) {
+                for (int c = 0; c < C; ++c) a.logits[(size_t)s * C + c] = lg[c];
+            } else if (MODE == MODE_TRAIN) {
+                float se = 0.0f;
+                for (int c = 0; c < C; ++c) se += __expf(lg[c] - mx);
+                const float lse = mx + __logf(se);
+                loss_acc += (lse - lg[label]) * invB;
+                for (int c = 0; c < C; ++c)
+                    dlog[c] = (__expf(lg[c] - lse) - (c == label ? 1.0f : 0.0f)) * invB * lscale;
+            } else {
+                for (int c = 0; c < C; ++c) dlog[c] = a.dlogits[(size_t)s * C + c];
+            }
+        }
+        if (MODE == MODE_FWD) continue;      // next iteration starts with a __syncthreads before xs reuse
+        __syncthreads();
+
+        // ---- head grads, dp, dz2 = mask * dp / L -> dz2 planes -----------------------------------------------
+        if (t < 16 * C) ghead0 = fmaf(dlog[t >> 4], pooled[t & 15], ghead0);
+        else if (t < 17 * C) ghead0 += dlog[t - 16 * C];
+        if (t + 128 < 17 * C) {
+            const int u = t + 128;
+            if (u < 16 * C) ghead1 = fmaf(dlog[u >> 4], pooled[u & 15], ghead1); else ghead1 += dlog[u - 16 * C];
+        }
+        if (t < 16) {
+            float v = 0.0f;
+            for (int c = 0; c < C; ++c) v = fmaf(whs[c * 16 + t], dlog[c], v);
+            gj[t] = v * invL;
+        }
+        __syncthreads();
+        {
+            float g[16];
+#pragma unroll
+            for (int c = 0; c < 16; ++c) g[c] = gj[c];
+#pragma unroll
+            for (int i = 0; i < TILES; ++i) {
+                const int l = i * 128 + t;
+                if (l < L) {
+                    uint32_t q[8];
+#pragma unroll
+                    for (int c = 0; c < 16; c += 2)
+                        q[c >> 1] = pack2<FP16>((mask[i] >> c) & 1u ? g[c] : 0.0f, (mask[i] >> (c + 1)) & 1u ? g[c + 1] : 0.0f);
+                    const int ro = (l + 8) * 16;
+                    *reinterpret_cast<uint4*>(smem + S::P_DZ2 + ro) = make_uint4(q[0], q[1], q[2], q[3]);
+                    *reinterpret_cast<uint4*>(smem + S::P_DZ2 + S::PLANE + ro) = make_uint4(q[4], q[5], q[6], q[7]);
+                }
+            }
+        }
+        fence_proxy_async_smem();
+        tc_fence_before_sync();
+        __syncthreads();
+
+        // ---- conv2 dgrad (reuses the forward accumulator columns) + conv2 wgrad -------------------------
+        if (t == 0) {
+            tc_fence_after_sync();
+            for (int i = 0; i < tiles; ++i)
+#pragma unroll
+                for (int k = 0; k < 5; ++k)
+                    mma_f16(tmem_base + i * 16, smem_desc(s_dz2 + (i * 128 + 10 - k) * 16, S::PLANE, 128),
+                            smem_desc(s_wt + (5 + k) * 512, 256, 128), ID_CONV, k > 0);
+            mma_commit(bar_dg);
+            const int chunks = tiles * 8;
+            for (int c = 0; c < chunks; ++c) {
+                const uint32_t acc = (it > 0 || c > 0) ? 1u : 0u;
+                const uint64_t bd = smem_desc(s_dz2 + (c * 16 + 8) * 16, 128, S::PLANE);
+                // M-group g = plane shifted by g rows (SBO = 16 B): rows (g, c8) = dW2[:, 8j+c8, g]
+                mma_f16(tmem_base + col_w, smem_desc(s_h1 + (c * 16 + 6) * 16, 128, 16), bd, ID_WG, acc);
+                mma_f16(tmem_base + col_w + 16, smem_desc(s_h1 + S::PLANE + (c * 16 + 6) * 16, 128, 16), bd, ID_WG, acc);
+            }
+        }
+        mbar_wait(bar_dg, par);
+        tc_fence_after_sync();
+
+        // ---- epilogue 2: dz1 = dh1 * (h1 > 0) -> dz1 planes ---------------------------------------------------
+#pragma unroll
+        for (int i = 0; i < TILES; ++i) {
+            if (i < tiles) {
+                uint32_t v[16];
+                tmem_ld16(tmem_lane + i * 16, v);
+                tmem_ld_wait();
+                const int l = i * 128 + t;
+                if (l < L) {
+                    const int ro = (l + 8) * 16;
+                    const uint4 ha = *reinterpret_cast<const uint4*>(smem + S::P_H1 + ro);
+                    const uint4 hb = *reinterpret_cast<const uint4*>(smem + S::P_H1 + S::PLANE + ro);
+                    const uint32_t hw[8] = {ha.x, ha.y, ha.z, ha.w, hb.x, hb.y, hb.z, hb.w};
+                    uint32_t q[8];
+#pragma unroll
+                    for (int c = 0; c < 16; c += 2) {
+                        const float2 h = unpack2<FP16>(hw[c >> 1]);
+                        q[c >> 1] = pack2<FP16>(h.x > 0.0f ? __uint_as_float(v[c]) : 0.0f,
+                                                h.y > 0.0f ? __uint_as_float(v[c + 1]) : 0.0f);
+                    }
+                    *reinterpret_cast<uint4*>(smem + S::P_DZ1 + ro) = make_uint4(q[0], q[1], q[2], q[3]);
+                    *reinterpret_cast<uint4*>(smem + S::P_DZ1 + S::PLANE + ro) = make_uint4(q[4], q[5], q[6], q[7]);
+                }
+            }
+        }
+        fence_proxy_async_smem();
+        tc_fence_before_sync();
+        __syncthreads();
+
+        // ---- conv1 wgrad + bias grads: D[k, n] = sum_l xcol[l, k] * [dz1 | dz2][l, n] -----------------------
+        if (t == 0) {
+            tc_fence_after_sync();
+            const int chunks = tiles * 8;
+            for (int c = 0; c < chunks; ++c)
+                mma_f16(tmem_base + col_b, smem_desc(s_xcol + (c * 16 + 8) * 16, 128, 16),
+                        smem_desc(s_dz1 + (c * 16 + 8) * 16, 128, S::PLANE), ID_WB, (it > 0 || c > 0) ? 1u : 0u);
+            mma_commit(bar_wg);
+        }
+    }
+
+    if (MODE != MODE_FWD && it > 0) {
+        // ---- read the weight-gradient accumulators out of TMEM once, add into the global buffer -----------
+        mbar_wait(bar_wg, (it - 1) & 1);
+        tc_fence_after_sync();
+        float* g = a.gacc;
+        const int r = t;                                  // accumulator row = TMEM lane (M = 128)
+        if (warp < 2) {
+            uint32_t v[32];
+            tmem_ld32(tmem_lane + col_w, v);
+            tmem_ld_wait();
+            const int k = r >> 3, c8 = r & 7;
+            if (k < 5) {
+#pragma unroll
+                for (int n = 0; n < 32; ++n) {
+                    const int co = n & 15, ci = (n >> 4) * 8 + c8;
+                    atomicAdd(g + TinyLayout::W2 + (co * 16 + ci) * 5 + k, __uint_as_float(v[n]));
+                }
+            }
+        }
+        if (warp == 0) {
+            uint32_t v[32];
+            tmem_ld32(tmem_lane + col_b, v);
+            tmem_ld_wait();
+            if (r < 7) {
+#pragma unroll
+                for (int c = 0; c < 16; ++c) atomicAdd(g + TinyLayout::W1 + c * 7 + r, __uint_as_float(v[c]));
+            } else if (r == 7) {
+#pragma unroll
+                for (int c = 0; c < 16; ++c) {
+                    atomicAdd(g + TinyLayout::B1 + c, __uint_as_float(v[c]));
+                    atomicAdd(g + TinyLayout::B2 + c, __uint_as_float(v[16 + c]));
+                }
+            }
+        }
+        if (t < 17 * C) atomicAdd(g + TinyLayout::WH + t, ghead0);
+        if (t + 128 < 17 * C) atomicAdd(g + TinyLayout::WH + t + 128, ghead1);
+    }
+
+    tc_fence_before_sync();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tmem_base, S::TMEM_COLS);
+
+    if (MODE == MODE_TRAIN) {
+        if (t == 0) atomicAdd(a.fstate + FS_LOSS_STEP, loss_acc);
+        __threadfence();
+        __syncthreads();
+        if (t == 0) {
+            const int tk = atomicAdd(a.ctrl + CTRL_TICKET, 1);
+            *is_last = (tk == (int)gridDim.x - 1);
+        }
+        __syncthreads();
+        if (*is_last) { __threadfence(); tiny_sgd_tail<kUThreads>(a, TinyLayout::total(C)); }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------
+template <int TILES, bool FP16, int MODE>
+static int launch_tiles_mode(const TinyArgs& a, cudaStream_t st) {
+    using S = USmem<TILES>;
+    const size_t smem = S::TOTAL;
+    // 2 CTAs per SM co-reside (smem ~69 KB, 128 TMEM columns each at TILES=4): while one waits on its
+    // MMAs the other runs its CUDA-core phases
+    int dev = 0;
+    CS_CUDA_OK(cudaGetDevice(&dev));
+    const int per_sm = (TILES <= 4) ? 2 : 1;
+    const int grid = a.B < num_sms() * per_sm ? a.B : num_sms() * per_sm;
+    static size_t configured[64] = {};          // one record per kernel instantiation
+    if (smem > configured[dev & 63]) {
+        CS_CUDA_OK(cudaFuncSetAttribute(tiny_umma_kernel<TILES, FP16, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured[dev & 63] = smem;
+    }
+    tiny_umma_kernel<TILES, FP16, MODE><<<grid, kUThreads, smem, st>>>(a);
+    CS_CUDA_OK(cudaGetLastError());
+    return CS_OK;
+}
+
+template <int TILES, bool FP16>
+static int launch_tiles(int mode, const TinyArgs& a, cudaStream_t st) {
+    if (mode == MODE_FWD) return launch_tiles_mode<TILES, FP16, MODE_FWD>(a, st);
+    if (mode == MODE_BWD) return launch_tiles_mode<TILES, FP16, MODE_BWD>(a, st);
+    return launch_tiles_mode<TILES, FP16, MODE_TRAIN>(a, st);
+}
+
+static int launch_umma(int mode, const TinyArgs& a, cudaStream_t st) {
+    CS_REQUIRE(tiny_umma_supported(a.L, a.C), "tcgen05 TinyECG path: unsupported L=%d C=%d", a.L, a.C);
+    CS_REQUIRE(a.B >= 1, "bad batch %d", a.B);
+    const bool fp16 = a.amp == CS_AMP_FP16;
+    if (a.L <= 512) return fp16 ? launch_tiles<4, true>(mode, a, st) : launch_tiles<4, false>(mode, a, st);
+    return fp16 ? launch_tiles<8, true>(mode, a, st) : launch_tiles<8, false>(mode, a, st);
+}
+
+int tiny_umma_forward(const TinyArgs& a, cudaStream_t st) { return launch_umma(MODE_FWD, a, st); }
+int tiny_umma_backward(const TinyArgs& a, cudaStream_t st) { return launch_umma(MODE_BWD, a, st); }
+int tiny_umma_train(const TinyArgs& a, cudaStream_t st) { return launch_umma(MODE_TRAIN, a, st); }
+size_t tiny_umma_smem_bytes(int L, int C) { return L <= 512 ? USmem<4>::TOTAL : USmem<8>::TOTAL; }
+
+bool tiny_umma_supported(int L, int C) {
+    static int sm100 = -1;
+    if (sm100 < 0) {
+        int dev = 0, major = 0;
+        sm100 = (cudaGetDevice(&dev) == cudaSuccess &&
+                 cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev) == cudaSuccess && major == 10) ? 1 : 0;
+    }
+    return sm100 == 1 && L >= 8 && L <= 1024 && C >= 1 && C <= kTinyMaxC;
+}
+
+}  // namespace cs
