@@ -27,6 +27,7 @@ _CUDA_SIGS = {
     "cs_device_is_sm100": (i32, []),
     "cs_gather_rows": (i32, [vp, vp, vp, vp, vp, i32, i32, i32, vp]),
     "cs_tiny_ecg_smem_bytes": (sz, [i32, i32, i32]),
+    "cs_tiny_ecg_scratch_floats": (sz, [i32]),
     "cs_tiny_ecg_forward": (i32, [vp, vp, i32, i32, i32, i32, vp, vp, i32, vp]),
     "cs_tiny_ecg_backward": (i32, [vp, vp, i32, i32, i32, i32, vp, vp, vp, i32, vp]),
     "cs_tiny_ecg_train_step": (i32, [vp, vp, vp, i32, i32, i32, i32, vp, vp, vp, vp, vp, f32, f32, f32,

@@ -110,7 +110,8 @@ class TinyTrainState:
         self.scaler = scaler or ScalerConfig(enabled=(amp == AMP_FP16))
         dev = params.device
         self.mom = torch.zeros_like(params)
-        self.gacc = torch.zeros_like(params)
+        self.gacc = torch.zeros(int(_lib.cuda_lib().cs_tiny_ecg_scratch_floats(num_classes)),
+                                dtype=torch.float32, device=dev)
         self.ctrl = torch.zeros(8, dtype=torch.int32, device=dev)
         self.fstate = torch.zeros(8, dtype=torch.float32, device=dev)
         self.fstate[FS_SCALE] = self.scaler.init_scale if self.scaler.enabled else 1.0

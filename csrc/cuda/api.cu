@@ -88,6 +88,8 @@ extern "C" {
 
 const char* cs_last_error(void) { return g_err; }
 int cs_version(void) { return 100; }
+/* debug: 32 x int64 device buffer receiving per-phase clock64 stamps of CTA 0 of the tcgen05 TinyECG kernel */
+void cs_debug_set_tiny_profile(void* buf) { g_tiny_prof = (long long*)buf; }
 
 int cs_device_is_sm100(void) {
     int dev = 0, major = 0;
@@ -99,6 +101,11 @@ int cs_device_is_sm100(void) {
 int cs_gather_rows(const float* x, const int64_t* y, const int64_t* idx, void* xo, int64_t* yo, int B, int L,
                    int out_bf16, cs_stream_t s) {
     return gather_rows(x, y, idx, xo, yo, B, L, out_bf16, ST(s));
+}
+
+size_t cs_tiny_ecg_scratch_floats(int C) {
+    const size_t a = tiny_umma_scratch_floats(), b = (size_t)TinyLayout::total(C) + 8;
+    return a > b ? a : b;
 }
 
 size_t cs_tiny_ecg_smem_bytes(int L, int C, int amp) {

@@ -14,6 +14,7 @@ struct TinyArgs {
     float* logits; const float* dlogits;
     float lr, momentum, wd; int use_scaler; float growth, backoff; int interval;
     int amp;
+    long long* prof;   // debug: per-phase clock64 stamps of CTA 0 (NULL in production)
 };
 
 int tiny_f32_forward(const TinyArgs& a, cudaStream_t st);
@@ -26,6 +27,8 @@ int tiny_umma_backward(const TinyArgs& a, cudaStream_t st);
 int tiny_umma_train(const TinyArgs& a, cudaStream_t st);
 size_t tiny_umma_smem_bytes(int L, int C);
 bool tiny_umma_supported(int L, int C);
+size_t tiny_umma_scratch_floats();
+extern long long* g_tiny_prof;   // set by cs_debug_set_tiny_profile
 
 // SGD / scaler tail shared by both paths; run by the last CTA of a training-step kernel.
 template <int THREADS>

@@ -25,14 +25,135 @@
 #include "tiny_ecg.cuh"
 #include "common/tcgen05.cuh"
 
+#include <stdlib.h>
+
 namespace cs {
 
 using namespace tc;
 
 constexpr int kUThreads = 128;
+long long* g_tiny_prof = nullptr;
+__device__ __forceinline__ unsigned long long gtimer() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
+#define TSTAMP(k) do { if (a.prof && blockIdx.x == 0 && threadIdx.x == 0) a.prof[k] = clock64(); } while (0)
+#define TAILSTAMP(k) do { if (a.prof && threadIdx.x == 0) a.prof[k] = (long long)gtimer(); } while (0)
 #ifndef CS_TINY_WGRAD_M
-#define CS_TINY_WGRAD_M 128      // M of the weight-gradient MMAs (128: row r -> TMEM lane r)
+#define CS_TINY_WGRAD_M 64       // M of the weight-gradient MMAs: 64 rows = 8 tap groups x 8 channels
 #endif
+// TMEM lane that holds accumulator row r: M=128 -> lane r; M=64 -> 16 lanes per 32-lane subpartition
+__device__ __forceinline__ int wgrad_row_of_thread(int t) {
+#if CS_TINY_WGRAD_M == 128
+    return t;
+#else
+    return (t & 31) < 16 ? (t >> 5) * 16 + (t & 15) : -1;
+#endif
+}
+
+// Gradient scratch of the training kernel: TMEM-shaped so each thread adds whole rows with 16-byte
+// vector reductions, and replicated kScratchReps times (CTA b uses replica b % reps) so that same-address
+// traffic in L2 is spread out.  The SGD tail sums the replicas and un-permutes.
+//   [0, 1280)      conv2 weight grad  row (k*8 + c8) x col (j*16 + co)      -> dW2[co][8j+c8][k]
+//   [1280, 1536)   bias MMA           row k x col n: n<16 dW1[n][k] (k<7), db1[n] (k=7); n>=16: db2[n-16] (k=7)
+//   [1536, 1672)   head weight + bias grads (17*C <= 136)
+constexpr int kScratchReps = 4;
+constexpr int kScratchStride = 1792;
+constexpr int kScrGB = 1280, kScrGH = 1536;
+__host__ __device__ inline int scratch_offset(int i) {     // flat parameter index -> scratch offset
+    if (i < TinyLayout::B1) return kScrGB + (i % 7) * 32 + i / 7;
+    if (i < TinyLayout::W2) return kScrGB + 7 * 32 + (i - TinyLayout::B1);
+    if (i < TinyLayout::B2) {
+        const int q = i - TinyLayout::W2, co = q / 80, ci = (q / 5) & 15, k = q % 5;
+        return (k * 8 + (ci & 7)) * 32 + (ci >> 3) * 16 + co;
+    }
+    if (i < TinyLayout::WH) return kScrGB + 7 * 32 + 16 + (i - TinyLayout::B2);
+    return kScrGH + (i - TinyLayout::WH);
+}
+__device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, float d) {
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
+// sum of SETS rotating 32-column accumulator sets (warp-collective TMEM loads)
+template <int SETS> __device__ __forceinline__ void load_sum_sets(uint32_t taddr, float (&out)[32]) {
+#pragma unroll
+    for (int n = 0; n < 32; ++n) out[n] = 0.0f;
+#pragma unroll
+    for (int q = 0; q < SETS; ++q) {
+        uint32_t v[32];
+        tmem_ld32(taddr + q * 32, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int n = 0; n < 32; ++n) out[n] += __uint_as_float(v[n]);
+    }
+}
+
+// Last-CTA tail of the tcgen05 training kernel.  Phase 1 sums the replicas in scratch order (fully
+// coalesced: consecutive threads read consecutive floats) into shared memory; phase 2 walks the
+// parameters in order (coalesced params / momentum), gathering its gradient from shared memory.
+// All global loads of a phase are issued before any dependent use: two L2 round trips in total.
+__device__ __forceinline__ void umma_sgd_tail(const TinyArgs& a, int P, float* sg /* smem, kScratchStride floats */) {
+    constexpr int NV = (TinyLayout::WH + 17 * kTinyMaxC + kUThreads - 1) / kUThreads;
+    constexpr int NS = kScratchStride / kUThreads;         // 14 scratch floats per thread
+    const int t = threadIdx.x;
+    const float4 fs = __ldcg(reinterpret_cast<const float4*>(a.fstate));     // loss_sum, scale, last, loss_step
+    const int4 cs4 = __ldcg(reinterpret_cast<const int4*>(a.ctrl));          // ticket, growth, steps, skipped
+    const float scale = a.use_scaler ? fs.y : 1.0f;
+    const float inv = 1.0f / scale;
+    {
+        float acc[NS];
+#pragma unroll
+        for (int j = 0; j < NS; ++j) acc[j] = 0.0f;
+#pragma unroll
+        for (int r = 0; r < kScratchReps; ++r)
+#pragma unroll
+            for (int j = 0; j < NS; ++j) acc[j] += __ldcg(a.gacc + r * kScratchStride + j * kUThreads + t);
+#pragma unroll
+        for (int j = 0; j < NS; ++j) sg[j * kUThreads + t] = acc[j];
+    }
+    float g[NV], p[NV], m[NV];
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+        const int i = t + j * kUThreads;
+        p[j] = 0.0f; m[j] = 0.0f;
+        if (i < P) { p[j] = a.params[i]; m[j] = a.mom[i]; }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+        const int i = t + j * kUThreads;
+        g[j] = i < P ? sg[scratch_offset(i)] * inv : 0.0f;
+    }
+    TAILSTAMP(42);
+    int bad = 0;
+#pragma unroll
+    for (int j = 0; j < NV; ++j) if (!finite_f(g[j])) bad = 1;
+    bad = __syncthreads_or(bad);
+    TAILSTAMP(43);
+    if (!bad) {
+#pragma unroll
+        for (int j = 0; j < NV; ++j) {
+            const int i = t + j * kUThreads;
+            if (i < P) {
+                const float mm = a.momentum * m[j] + (g[j] + a.wd * p[j]);
+                a.mom[i] = mm;
+                a.params[i] = p[j] - a.lr * mm;
+            }
+        }
+    }
+    TAILSTAMP(44);
+    float4* z = reinterpret_cast<float4*>(a.gacc);
+    for (int i = t; i < kScratchReps * kScratchStride / 4; i += kUThreads) z[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    TAILSTAMP(45);
+    if (t == 0) {
+        float nscale = fs.y;
+        int growth = cs4.y;
+        if (a.use_scaler) {
+            if (bad) { nscale = scale * a.backoff; growth = 0; }
+            else if (++growth >= a.interval) { nscale = scale * a.growth; growth = 0; }
+        }
+        *reinterpret_cast<float4*>(a.fstate) = make_float4(fs.x + fs.w, nscale, fs.w, 0.0f);
+        *reinterpret_cast<int4*>(a.ctrl) = make_int4(0, growth, cs4.z + 1, cs4.w + (bad ? 1 : 0));
+        a.ctrl[CTRL_FOUND_INF] = bad;
+    }
+}
 
 template <int TILES> struct USmem {
     static constexpr int ROWS = TILES * 128 + 16;          // 8 halo rows on top, >= 8 below
@@ -48,7 +169,8 @@ template <int TILES> struct USmem {
     static constexpr int P_DZ1 = OFF_PLANES, P_DZ2 = P_DZ1 + 2 * PLANE, P_H1 = P_DZ2 + 2 * PLANE,
                          P_XCOL = P_H1 + 2 * PLANE;
     static constexpr int TOTAL = P_XCOL + PLANE + 512;     // slack: shifted operands read past the end
-    static constexpr int TMEM_COLS = (16 * TILES + 64) <= 128 ? 128 : 256;
+    // conv accumulators 16*TILES | conv2-wgrad 2 rotating sets x 2 planes x 16 | bias-MMA 4 rotating sets x 32
+    static constexpr int TMEM_COLS = (16 * TILES + 64 + 128) <= 256 ? 256 : 512;
 };
 
 template <bool FP16> __device__ __forceinline__ uint32_t pack2(float a, float b) {
@@ -101,6 +223,8 @@ __global__ void __launch_bounds__(kUThreads) tiny_umma_kernel(TinyArgs a) {
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     const int L = a.L, C = a.C;
     const int tiles = (L + 127) >> 7;
+    TSTAMP(0);
+    if (a.prof && threadIdx.x == 0) a.prof[64 + 2 * blockIdx.x] = (long long)gtimer();
 
     uint64_t* bar_fwd = reinterpret_cast<uint64_t*>(smem + S::OFF_BAR);
     uint64_t* bar_dg = bar_fwd + 1;
@@ -115,24 +239,56 @@ __global__ void __launch_bounds__(kUThreads) tiny_umma_kernel(TinyArgs a) {
     float* xs = reinterpret_cast<float*>(smem + S::OFF_XS);
     const float* prm = a.params;
 
+    // ---- the first window's loads are issued before anything else: they overlap the whole prologue ----
+    float xin[TILES];
+    int label = 0;
+    auto prefetch_sample = [&](int s) {
+        const int64_t row = a.idx ? a.idx[s] : (int64_t)s;
+#pragma unroll
+        for (int i = 0; i < TILES; ++i) {
+            const int l = i * 128 + t;
+            xin[i] = 0.0f;
+            if (l < L) xin[i] = a.x_bf16 ? __bfloat162float(((const __nv_bfloat16*)a.x)[row * L + l])
+                                         : __ldg((const float*)a.x + row * L + l);
+        }
+        if (MODE == MODE_TRAIN && warp == 0) label = (int)a.y[row];
+    };
+    if ((int)blockIdx.x < a.B) prefetch_sample(blockIdx.x);
+
     // ---- one-time set-up ------------------------------------------------------------------------
     {   // zero every operand plane + xs: halo rows / tail rows / slack stay zero (and finite) forever
         uint4* z = reinterpret_cast<uint4*>(smem + S::OFF_XS);
         const int n16 = (S::TOTAL - S::OFF_XS) / 16;
         for (int i = t; i < n16; i += kUThreads) z[i] = make_uint4(0, 0, 0, 0);
     }
-    for (int i = t; i < 112; i += kUThreads) w1s[i] = prm[TinyLayout::W1 + i];
-    if (t < 16) { b1s[t] = prm[TinyLayout::B1 + t]; b2s[t] = prm[TinyLayout::B2 + t]; }
-    for (int i = t; i < 16 * C; i += kUThreads) whs[i] = prm[TinyLayout::WH + i];
-    if (t < C) bhs[t] = prm[TinyLayout::bh(C) + t];
-    for (int i = t; i < 1280; i += kUThreads) {        // W2 [co][ci][k] -> K-major 16x16 tiles per tap
-        const int co = i / 80, ci = (i / 5) & 15, k = i % 5;
-        const uint16_t h = pack1<FP16>(prm[TinyLayout::W2 + i]);
-        // forward tile k:  B[n = co][kk = ci];  dgrad tile 5+k:  B[n = ci][kk = co]
-        const int off_f = (co & 7) * 16 + (co >> 3) * 128 + (ci >> 3) * 256 + (ci & 7) * 2;
-        const int off_d = (ci & 7) * 16 + (ci >> 3) * 128 + (co >> 3) * 256 + (co & 7) * 2;
-        *reinterpret_cast<uint16_t*>(wt + k * 512 + off_f) = h;
-        if (MODE != MODE_FWD) *reinterpret_cast<uint16_t*>(wt + (5 + k) * 512 + off_d) = h;
+    // Programmatic dependent launch: everything above (window prefetch, smem clear) may run while the
+    // previous step's kernel is still finishing; parameters / scaler state are read only after it has
+    // completed and flushed.  (No-op when the launch carries no programmatic dependency.)
+    if (MODE == MODE_TRAIN) asm volatile("griddepcontrol.wait;" ::: "memory");
+    {   // all parameter loads are issued before any is consumed: ONE L2 round trip for the prologue
+        const int P = TinyLayout::total(C);
+        constexpr int NV = (TinyLayout::WH + 17 * kTinyMaxC + kUThreads - 1) / kUThreads;
+        float pv[NV];
+#pragma unroll
+        for (int j = 0; j < NV; ++j) { const int i = t + j * kUThreads; pv[j] = i < P ? __ldg(prm + i) : 0.0f; }
+#pragma unroll
+        for (int j = 0; j < NV; ++j) {
+            const int i = t + j * kUThreads;
+            if (i < TinyLayout::B1) w1s[i] = pv[j];
+            else if (i < TinyLayout::W2) b1s[i - TinyLayout::B1] = pv[j];
+            else if (i < TinyLayout::B2) {          // W2 [co][ci][k] -> K-major 16x16 operand tiles per tap
+                const int q = i - TinyLayout::W2;
+                const int co = q / 80, ci = (q / 5) & 15, k = q % 5;
+                const uint16_t h = pack1<FP16>(pv[j]);
+                // forward tile k:  B[n = co][kk = ci];  dgrad tile 5+k:  B[n = ci][kk = co]
+                const int off_f = (co & 7) * 16 + (co >> 3) * 128 + (ci >> 3) * 256 + (ci & 7) * 2;
+                const int off_d = (ci & 7) * 16 + (ci >> 3) * 128 + (co >> 3) * 256 + (co & 7) * 2;
+                *reinterpret_cast<uint16_t*>(wt + k * 512 + off_f) = h;
+                if (MODE != MODE_FWD) *reinterpret_cast<uint16_t*>(wt + (5 + k) * 512 + off_d) = h;
+            } else if (i < TinyLayout::WH) b2s[i - TinyLayout::B2] = pv[j];
+            else if (i < TinyLayout::WH + 16 * C) whs[i - TinyLayout::WH] = pv[j];
+            else if (i < P) bhs[i - TinyLayout::WH - 16 * C] = pv[j];
+        }
     }
     if (t == 0) {
         mbar_init(bar_fwd, 1); mbar_init(bar_dg, 1); mbar_init(bar_wg, 1);
@@ -144,8 +300,11 @@ __global__ void __launch_bounds__(kUThreads) tiny_umma_kernel(TinyArgs a) {
     __syncthreads();
     tc_fence_after_sync();
     const uint32_t tmem_base = *tmem_slot;
+    // let the next step's grid start its own prologue on SMs as they drain
+    if (MODE == MODE_TRAIN) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    TSTAMP(1);
     const uint32_t tmem_lane = tmem_base + ((uint32_t)(warp * 32) << 16);
-    const uint32_t col_w = 16 * TILES, col_b = 16 * TILES + 32;
+    const uint32_t col_w = 16 * TILES, col_b = 16 * TILES + 64;
 
     const uint32_t s_base = smem_u32(smem);
     const uint32_t s_dz1 = s_base + S::P_DZ1, s_dz2 = s_base + S::P_DZ2, s_h1 = s_base + S::P_H1,
@@ -162,23 +321,14 @@ __global__ void __launch_bounds__(kUThreads) tiny_umma_kernel(TinyArgs a) {
 
     for (int s = blockIdx.x; s < a.B; s += gridDim.x, ++it) {
         const uint32_t par = it & 1;
-        const int64_t row = a.idx ? a.idx[s] : (int64_t)s;
-        // ---- P1: window -> xs (rounded to the operand type, as autocast would feed conv1) --------
-        float xin[TILES];
-#pragma unroll
-        for (int i = 0; i < TILES; ++i) {
-            const int l = i * 128 + t;
-            float v = 0.0f;
-            if (l < L) v = a.x_bf16 ? __bfloat162float(((const __nv_bfloat16*)a.x)[row * L + l])
-                                    : __ldg((const float*)a.x + row * L + l);
-            xin[i] = round_half<FP16>(v);
-        }
-        int label = 0;
-        if (MODE == MODE_TRAIN && t == 0) label = (int)a.y[row];
+        // ---- P1: prefetched window -> xs (rounded to the operand type, as autocast would feed conv1) ----
+        const int cur_label = label;
         if (MODE != MODE_FWD && it > 0) mbar_wait(bar_wg, par ^ 1);   // previous sample's MMAs released the planes
 #pragma unroll
-        for (int i = 0; i < TILES; ++i) { const int l = i * 128 + t; if (l < L) xs[l + 3] = xin[i]; }
+        for (int i = 0; i < TILES; ++i) { const int l = i * 128 + t; if (l < L) xs[l + 3] = round_half<FP16>(xin[i]); }
+        if (s + (int)gridDim.x < a.B) prefetch_sample(s + gridDim.x);   // next window loads during this one
         __syncthreads();
+        if (it == 0) TSTAMP(2);
 
         // ---- P2: conv1 + ReLU on FFMA -> h1 planes; im2col(x)+ones -> xcol plane ------------------
         {
@@ -221,17 +371,23 @@ __global__ void __launch_bounds__(kUThreads) tiny_umma_kernel(TinyArgs a) {
         __syncthreads();
 
         // ---- conv2 forward on the tensor core ---------------------------------------------------------
+        if (it == 0) TSTAMP(3);
         if (t == 0) {
             tc_fence_after_sync();
-            for (int i = 0; i < tiles; ++i)
+            // descriptors differ only in the start-address field (16-byte units = plane rows)
+            const uint64_t a0 = smem_desc(s_h1 + 6 * 16, S::PLANE, 128);
+            const uint64_t b0 = smem_desc(s_wt, 256, 128);
+            // tap-outer / tile-inner: back-to-back MMAs never accumulate into the same TMEM tile
 #pragma unroll
-                for (int k = 0; k < 5; ++k)
-                    mma_f16(tmem_base + i * 16, smem_desc(s_h1 + (i * 128 + 6 + k) * 16, S::PLANE, 128),
-                            smem_desc(s_wt + k * 512, 256, 128), ID_CONV, k > 0);
+            for (int k = 0; k < 5; ++k)
+                for (int i = 0; i < tiles; ++i)
+                    mma_f16(tmem_base + i * 16, a0 + (uint64_t)(i * 128 + k), b0 + (uint64_t)(k * 32), ID_CONV, k > 0);
             mma_commit(bar_fwd);
         }
+        if (it == 0) TSTAMP(4);
         mbar_wait(bar_fwd, par);
         tc_fence_after_sync();
+        if (it == 0) TSTAMP(5);
 
         // ---- epilogue 1: bias + ReLU + pool partials, ReLU mask kept in registers --------------------
         float pool[16];
@@ -261,32 +417,37 @@ __global__ void __launch_bounds__(kUThreads) tiny_umma_kernel(TinyArgs a) {
         __syncthreads();
         if (t < 16) pooled[t] = (red[t] + red[16 + t] + red[32 + t] + red[48 + t]) * invL;
         __syncthreads();
+        if (it == 0) TSTAMP(6);
 
         // ---- head + cross entropy ------------------------------------------------------------------------
-        if (t == 0) {
-            float lg[kTinyMaxC];
-            float mx = -3.0e38f;
-            for (int c = 0; c < C; ++c) {
-                float v = bhs[c];
+        if (warp == 0) {
+            // lane c < C owns class c: logit, then a warp-shuffle softmax over the first C lanes
+            float lg = -3.0e38f;
+            if (lane < C) {
+                lg = bhs[lane];
 #pragma unroll
-                for (int j = 0; j < 16; ++j) v = fmaf(whs[c * 16 + j], pooled[j], v);
-                lg[c] = v; mx = fmaxf(mx, v);
+                for (int j = 0; j < 16; ++j) lg = fmaf(whs[lane * 16 + j], pooled[j], lg);
             }
             if (MODE == MODE_FWD) {
-                for (int c = 0; c < C; ++c) a.logits[(size_t)s * C + c] = lg[c];
+                if (lane < C) a.logits[(size_t)s * C + lane] = lg;
             } else if (MODE == MODE_TRAIN) {
-                float se = 0.0f;
-                for (int c = 0; c < C; ++c) se += __expf(lg[c] - mx);
+                float mx = lg;
+#pragma unroll
+                for (int o = 4; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+                float se = lane < C ? __expf(lg - mx) : 0.0f;
+#pragma unroll
+                for (int o = 4; o > 0; o >>= 1) se += __shfl_xor_sync(0xffffffffu, se, o);
                 const float lse = mx + __logf(se);
-                loss_acc += (lse - lg[label]) * invB;
-                for (int c = 0; c < C; ++c)
-                    dlog[c] = (__expf(lg[c] - lse) - (c == label ? 1.0f : 0.0f)) * invB * lscale;
+                const float lg_label = __shfl_sync(0xffffffffu, lg, cur_label & 7);
+                if (lane == 0) loss_acc += (lse - lg_label) * invB;
+                if (lane < C) dlog[lane] = (__expf(lg - lse) - (lane == cur_label ? 1.0f : 0.0f)) * invB * lscale;
             } else {
-                for (int c = 0; c < C; ++c) dlog[c] = a.dlogits[(size_t)s * C + c];
+                if (lane < C) dlog[lane] = a.dlogits[(size_t)s * C + lane];
             }
         }
         if (MODE == MODE_FWD) continue;      // next iteration starts with a __syncthreads before xs reuse
         __syncthreads();
+        if (it == 0) TSTAMP(7);
 
         // ---- head grads, dp, dz2 = mask * dp / L -> dz2 planes -----------------------------------------------
         if (t < 16 * C) ghead0 = fmaf(dlog[t >> 4], pooled[t & 15], ghead0);
@@ -324,25 +485,34 @@ __global__ void __launch_bounds__(kUThreads) tiny_umma_kernel(TinyArgs a) {
         __syncthreads();
 
         // ---- conv2 dgrad (reuses the forward accumulator columns) + conv2 wgrad -------------------------
+        if (it == 0) TSTAMP(8);
         if (t == 0) {
             tc_fence_after_sync();
-            for (int i = 0; i < tiles; ++i)
+            const uint64_t a0 = smem_desc(s_dz2 + 10 * 16, S::PLANE, 128);
+            const uint64_t b0 = smem_desc(s_wt + 5 * 512, 256, 128);
 #pragma unroll
-                for (int k = 0; k < 5; ++k)
-                    mma_f16(tmem_base + i * 16, smem_desc(s_dz2 + (i * 128 + 10 - k) * 16, S::PLANE, 128),
-                            smem_desc(s_wt + (5 + k) * 512, 256, 128), ID_CONV, k > 0);
+            for (int k = 0; k < 5; ++k)
+                for (int i = 0; i < tiles; ++i)
+                    mma_f16(tmem_base + i * 16, a0 + (uint64_t)(i * 128 - k), b0 + (uint64_t)(k * 32), ID_CONV, k > 0);
             mma_commit(bar_dg);
+            // conv2 wgrad: M-group g = plane shifted by g rows (SBO = 16 B): rows (g, c8) = dW2[:, 8j+c8, g]
             const int chunks = tiles * 8;
+            const uint64_t wa0 = smem_desc(s_h1 + 6 * 16, 128, 16);
+            const uint64_t wa1 = smem_desc(s_h1 + S::PLANE + 6 * 16, 128, 16);
+            const uint64_t wb = smem_desc(s_dz2 + 8 * 16, 128, S::PLANE);
+            // two rotating accumulator sets (even / odd chunks): 4 independent MMAs between dependent ones
+#pragma unroll 4
             for (int c = 0; c < chunks; ++c) {
-                const uint32_t acc = (it > 0 || c > 0) ? 1u : 0u;
-                const uint64_t bd = smem_desc(s_dz2 + (c * 16 + 8) * 16, 128, S::PLANE);
-                // M-group g = plane shifted by g rows (SBO = 16 B): rows (g, c8) = dW2[:, 8j+c8, g]
-                mma_f16(tmem_base + col_w, smem_desc(s_h1 + (c * 16 + 6) * 16, 128, 16), bd, ID_WG, acc);
-                mma_f16(tmem_base + col_w + 16, smem_desc(s_h1 + S::PLANE + (c * 16 + 6) * 16, 128, 16), bd, ID_WG, acc);
+                const uint32_t acc = (it > 0 || c >= 2) ? 1u : 0u;
+                const uint32_t d = tmem_base + col_w + (c & 1) * 32;
+                mma_f16(d, wa0 + (uint64_t)(c * 16), wb + (uint64_t)(c * 16), ID_WG, acc);
+                mma_f16(d + 16, wa1 + (uint64_t)(c * 16), wb + (uint64_t)(c * 16), ID_WG, acc);
             }
         }
+        if (it == 0) TSTAMP(9);
         mbar_wait(bar_dg, par);
         tc_fence_after_sync();
+        if (it == 0) TSTAMP(10);
 
         // ---- epilogue 2: dz1 = dh1 * (h1 > 0) -> dz1 planes ---------------------------------------------------
 #pragma unroll
@@ -374,57 +544,86 @@ __global__ void __launch_bounds__(kUThreads) tiny_umma_kernel(TinyArgs a) {
         __syncthreads();
 
         // ---- conv1 wgrad + bias grads: D[k, n] = sum_l xcol[l, k] * [dz1 | dz2][l, n] -----------------------
+        if (it == 0) TSTAMP(11);
         if (t == 0) {
             tc_fence_after_sync();
             const int chunks = tiles * 8;
-            for (int c = 0; c < chunks; ++c)
-                mma_f16(tmem_base + col_b, smem_desc(s_xcol + (c * 16 + 8) * 16, 128, 16),
-                        smem_desc(s_dz1 + (c * 16 + 8) * 16, 128, S::PLANE), ID_WB, (it > 0 || c > 0) ? 1u : 0u);
+            const uint64_t xa = smem_desc(s_xcol + 8 * 16, 128, 16);
+            const uint64_t xb = smem_desc(s_dz1 + 8 * 16, 128, S::PLANE);
+#pragma unroll 4
+            for (int c = 0; c < chunks; ++c)       // four rotating accumulator sets
+                mma_f16(tmem_base + col_b + (c & 3) * 32, xa + (uint64_t)(c * 16), xb + (uint64_t)(c * 16), ID_WB,
+                        (it > 0 || c >= 4) ? 1u : 0u);
             mma_commit(bar_wg);
         }
+        if (it == 0) TSTAMP(12);
     }
 
     if (MODE != MODE_FWD && it > 0) {
         // ---- read the weight-gradient accumulators out of TMEM once, add into the global buffer -----------
         mbar_wait(bar_wg, (it - 1) & 1);
         tc_fence_after_sync();
-        float* g = a.gacc;
-        const int r = t;                                  // accumulator row = TMEM lane (M = 128)
-        if (warp < 2) {
-            uint32_t v[32];
-            tmem_ld32(tmem_lane + col_w, v);
-            tmem_ld_wait();
-            const int k = r >> 3, c8 = r & 7;
-            if (k < 5) {
+        TSTAMP(13);
+        const int r = wgrad_row_of_thread(t);             // accumulator row held by this thread's TMEM lane
+        constexpr int kWarpsW = CS_TINY_WGRAD_M == 128 ? 2 : 3;   // warps whose lanes hold rows < 40
+        if (MODE == MODE_TRAIN) {
+            float* g = a.gacc + (blockIdx.x % kScratchReps) * kScratchStride;
+            if (warp < kWarpsW) {
+                float v[32];
+                load_sum_sets<2>(tmem_lane + col_w, v);
+                if (r >= 0 && r < 40) {
 #pragma unroll
-                for (int n = 0; n < 32; ++n) {
-                    const int co = n & 15, ci = (n >> 4) * 8 + c8;
-                    atomicAdd(g + TinyLayout::W2 + (co * 16 + ci) * 5 + k, __uint_as_float(v[n]));
+                    for (int n = 0; n < 32; n += 4) red_add_v4(g + r * 32 + n, v[n], v[n + 1], v[n + 2], v[n + 3]);
                 }
             }
-        }
-        if (warp == 0) {
-            uint32_t v[32];
-            tmem_ld32(tmem_lane + col_b, v);
-            tmem_ld_wait();
-            if (r < 7) {
+            if (warp == 0) {
+                float v[32];
+                load_sum_sets<4>(tmem_lane + col_b, v);
+                if (r >= 0 && r < 8) {
 #pragma unroll
-                for (int c = 0; c < 16; ++c) atomicAdd(g + TinyLayout::W1 + c * 7 + r, __uint_as_float(v[c]));
-            } else if (r == 7) {
-#pragma unroll
-                for (int c = 0; c < 16; ++c) {
-                    atomicAdd(g + TinyLayout::B1 + c, __uint_as_float(v[c]));
-                    atomicAdd(g + TinyLayout::B2 + c, __uint_as_float(v[16 + c]));
+                    for (int n = 0; n < 32; n += 4) red_add_v4(g + kScrGB + r * 32 + n, v[n], v[n + 1], v[n + 2], v[n + 3]);
                 }
             }
+            if (t < 17 * C) atomicAdd(g + kScrGH + t, ghead0);
+            if (t + 128 < 17 * C) atomicAdd(g + kScrGH + t + 128, ghead1);
+        } else {
+            float* g = a.gacc;                            // MODE_BWD: plain parameter-order gradient
+            if (warp < kWarpsW) {
+                float v[32];
+                load_sum_sets<2>(tmem_lane + col_w, v);
+                const int k = r >> 3, c8 = r & 7;
+                if (r >= 0 && r < 40) {
+#pragma unroll
+                    for (int n = 0; n < 32; ++n) {
+                        const int co = n & 15, ci = (n >> 4) * 8 + c8;
+                        atomicAdd(g + TinyLayout::W2 + (co * 16 + ci) * 5 + k, v[n]);
+                    }
+                }
+            }
+            if (warp == 0) {
+                float v[32];
+                load_sum_sets<4>(tmem_lane + col_b, v);
+                if (r >= 0 && r < 7) {
+#pragma unroll
+                    for (int c = 0; c < 16; ++c) atomicAdd(g + TinyLayout::W1 + c * 7 + r, v[c]);
+                } else if (r == 7) {
+#pragma unroll
+                    for (int c = 0; c < 16; ++c) {
+                        atomicAdd(g + TinyLayout::B1 + c, v[c]);
+                        atomicAdd(g + TinyLayout::B2 + c, v[16 + c]);
+                    }
+                }
+            }
+            if (t < 17 * C) atomicAdd(g + TinyLayout::WH + t, ghead0);
+            if (t + 128 < 17 * C) atomicAdd(g + TinyLayout::WH + t + 128, ghead1);
         }
-        if (t < 17 * C) atomicAdd(g + TinyLayout::WH + t, ghead0);
-        if (t + 128 < 17 * C) atomicAdd(g + TinyLayout::WH + t + 128, ghead1);
     }
+    TSTAMP(14);
 
     tc_fence_before_sync();
     __syncthreads();
     if (warp == 0) tmem_dealloc(tmem_base, S::TMEM_COLS);
+    TSTAMP(15);
 
     if (MODE == MODE_TRAIN) {
         if (t == 0) atomicAdd(a.fstate + FS_LOSS_STEP, loss_acc);
@@ -435,7 +634,12 @@ __global__ void __launch_bounds__(kUThreads) tiny_umma_kernel(TinyArgs a) {
             *is_last = (tk == (int)gridDim.x - 1);
         }
         __syncthreads();
-        if (*is_last) { __threadfence(); tiny_sgd_tail<kUThreads>(a, TinyLayout::total(C)); }
+        TSTAMP(16);
+        if (a.prof && threadIdx.x == 0) a.prof[64 + 2 * blockIdx.x + 1] = (long long)gtimer();
+        if (*is_last) {
+            __threadfence(); TAILSTAMP(46); umma_sgd_tail(a, TinyLayout::total(C), reinterpret_cast<float*>(smem + S::OFF_PLANES));
+            if (a.prof && threadIdx.x == 0) { a.prof[40] = (long long)gtimer(); a.prof[41] = blockIdx.x; }
+        }
     }
 }
 
@@ -455,8 +659,19 @@ static int launch_tiles_mode(const TinyArgs& a, cudaStream_t st) {
         CS_CUDA_OK(cudaFuncSetAttribute(tiny_umma_kernel<TILES, FP16, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured[dev & 63] = smem;
     }
-    tiny_umma_kernel<TILES, FP16, MODE><<<grid, kUThreads, smem, st>>>(a);
-    CS_CUDA_OK(cudaGetLastError());
+    static const bool use_pdl = []() { const char* e = getenv("CS_TINY_PDL"); return !(e && e[0] == '0'); }();
+    if (MODE == MODE_TRAIN && use_pdl) {
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(grid); cfg.blockDim = dim3(kUThreads); cfg.dynamicSmemBytes = smem; cfg.stream = st;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = attr; cfg.numAttrs = 1;
+        CS_CUDA_OK(cudaLaunchKernelEx(&cfg, tiny_umma_kernel<TILES, FP16, MODE>, a));
+    } else {
+        tiny_umma_kernel<TILES, FP16, MODE><<<grid, kUThreads, smem, st>>>(a);
+        CS_CUDA_OK(cudaGetLastError());
+    }
     return CS_OK;
 }
 
@@ -471,6 +686,7 @@ static int launch_umma(int mode, const TinyArgs& a, cudaStream_t st) {
     CS_REQUIRE(tiny_umma_supported(a.L, a.C), "tcgen05 TinyECG path: unsupported L=%d C=%d", a.L, a.C);
     CS_REQUIRE(a.B >= 1, "bad batch %d", a.B);
     const bool fp16 = a.amp == CS_AMP_FP16;
+    const_cast<TinyArgs&>(a).prof = g_tiny_prof;
     if (a.L <= 512) return fp16 ? launch_tiles<4, true>(mode, a, st) : launch_tiles<4, false>(mode, a, st);
     return fp16 ? launch_tiles<8, true>(mode, a, st) : launch_tiles<8, false>(mode, a, st);
 }
@@ -478,6 +694,7 @@ static int launch_umma(int mode, const TinyArgs& a, cudaStream_t st) {
 int tiny_umma_forward(const TinyArgs& a, cudaStream_t st) { return launch_umma(MODE_FWD, a, st); }
 int tiny_umma_backward(const TinyArgs& a, cudaStream_t st) { return launch_umma(MODE_BWD, a, st); }
 int tiny_umma_train(const TinyArgs& a, cudaStream_t st) { return launch_umma(MODE_TRAIN, a, st); }
+size_t tiny_umma_scratch_floats() { return (size_t)kScratchReps * kScratchStride; }
 size_t tiny_umma_smem_bytes(int L, int C) { return L <= 512 ? USmem<4>::TOTAL : USmem<8>::TOTAL; }
 
 bool tiny_umma_supported(int L, int C) {

@@ -59,6 +59,10 @@ int cs_gather_rows(const float* x, const int64_t* y, const int64_t* idx, void* x
 /* bytes of dynamic shared memory the fused kernels need for window length L (0 if unsupported) */
 size_t cs_tiny_ecg_smem_bytes(int L, int C, int amp);
 
+/* floats the `gacc` gradient scratch of cs_tiny_ecg_train_step must hold (zeroed once by the caller;
+ * every step leaves it zero).  The tcgen05 kernel keeps 8 TMEM-shaped replicas there. */
+size_t cs_tiny_ecg_scratch_floats(int C);
+
 /* logits[B,C] = TinyECG(x) */
 int cs_tiny_ecg_forward(const void* x, const int64_t* idx, int x_bf16, int B, int L, int C,
                         const float* params, float* logits, int amp, cs_stream_t stream);
@@ -71,8 +75,8 @@ int cs_tiny_ecg_backward(const void* x, const int64_t* idx, int x_bf16, int B, i
 /* One whole local training step in ONE launch: gather + forward + mean cross-entropy (x loss
  * scale) + backward + grad unscale/inf-check + SGD-momentum update + scaler update.
  *   y      labels, indexed like x (y[idx[b]] or y[b])
- *   mom    momentum buffer  [P]        gacc   gradient scratch [P], must be zero on first use;
- *                                              the kernel leaves it zero again
+ *   mom    momentum buffer  [P]        gacc   gradient scratch, cs_tiny_ecg_scratch_floats(C) floats,
+ *                                              zero on first use; the kernel leaves it zero again
  *   ctrl   int32[8]  {ticket, growth_tracker, steps_done, skipped_steps, found_inf, ...}
  *   fstate fp32[8]   {loss_sum, loss_scale, last_loss, loss_step_scratch, ...}
  * SGD: buf = momentum*buf + (g + wd*p); p -= lr*buf            (torch.optim.SGD, ref :181)
