@@ -87,6 +87,22 @@ int cs_tiny_ecg_train_step(const void* x, const int64_t* y, const int64_t* idx, 
                            int amp, int use_scaler, float growth, float backoff,
                            int growth_interval, cs_stream_t stream);
 
+/* The same training step for callers that cannot allocate device memory (a client library living
+ * inside another framework's pre-reserved memory pool, a control loop that must not hit the device
+ * synchronisation of cudaMalloc/cudaFree, a bare C/ctypes driver that only passes inputs and outputs).
+ * This entry point has no counterpart in the reference.
+ * The gradient scratch is a CS_TINY_NOALLOC_SCRATCH_FLOATS-float (28 KiB) __device__ array built into
+ * the library, resident on every GPU that loads it until the process exits; C > 8 (more scratch than
+ * the array holds) is rejected with an error.  The first call on a device looks the array up — issue
+ * it outside any stream capture.  All calls share the array and each clears what it uses first, so
+ * calls that overlap on one GPU race: keep them on one stream.  Allocates nothing. */
+#define CS_TINY_NOALLOC_SCRATCH_FLOATS 7168
+int cs_tiny_ecg_train_step_noalloc(const void* x, const int64_t* y, const int64_t* idx, int x_bf16,
+                                   int B, int L, int C, float* params, float* mom, int32_t* ctrl,
+                                   float* fstate, float lr, float momentum, float wd, int amp,
+                                   int use_scaler, float growth, float backoff, int growth_interval,
+                                   cs_stream_t stream);
+
 /* ---------------------------------------------------------------------------------------------
  * K5   head-less cross entropy + loss scale, and AMP unscale / inf-check / scale update
  *      ref: F.cross_entropy (:107,:123), GradScaler (:125-127)
