@@ -13,22 +13,28 @@ import torch
 import torch.nn as nn
 
 from ..ops.conv1d import Conv1dB200
-from ..ops.norm_act import BNReLU1d, global_avg_pool1d
+from ..ops.norm_act import BNReLU1d, avg_pool2, global_avg_pool1d
 
 
 class BasicBlock1D(nn.Module):
-    def __init__(self, cin: int, cout: int, k: int = 7, stride: int = 1):
+    """conv-BN-ReLU-conv-BN(+skip)-ReLU; ``down`` halves the length with a 2:1 average pool first (all
+    convolutions stay stride 1, which is what the shifted-descriptor implicit GEMM implements)."""
+
+    def __init__(self, cin: int, cout: int, k: int = 7, down: bool = False):
         super().__init__()
-        self.conv1 = Conv1dB200(cin, cout, k, padding=k // 2, stride=stride, bias=False)
+        self.pool = down
+        self.conv1 = Conv1dB200(cin, cout, k, padding=k // 2, bias=False)
         self.bn1 = BNReLU1d(cout, relu=True)
         self.conv2 = Conv1dB200(cout, cout, k, padding=k // 2, bias=False)
         self.bn2 = BNReLU1d(cout, relu=True)  # ReLU applied after the residual add (fused)
         self.down = None
-        if cin != cout or stride != 1:
-            self.down = Conv1dB200(cin, cout, 1, padding=0, stride=stride, bias=False)
+        if cin != cout:
+            self.down = Conv1dB200(cin, cout, 1, padding=0, bias=False)
             self.down_bn = BNReLU1d(cout, relu=False)
 
     def forward(self, x):
+        if self.pool:
+            x = avg_pool2(x)
         idn = x if self.down is None else self.down_bn(self.down(x))
         y = self.bn1(self.conv1(x))
         return self.bn2(self.conv2(y), residual=idn)
@@ -43,7 +49,7 @@ class ResNet1DWide(nn.Module):
         layers, cin = [], stem
         for i, w in enumerate(widths):
             for b in range(blocks_per_stage):
-                layers.append(BasicBlock1D(cin, w, k=k, stride=2 if (b == 0 and i > 0) else 1))
+                layers.append(BasicBlock1D(cin, w, k=k, down=(b == 0 and i > 0)))
                 cin = w
         self.layers = nn.Sequential(*layers)
         self.head = nn.Linear(cin, num_classes)

@@ -1,0 +1,135 @@
+"""tcgen05 implicit-GEMM conv1d (fwd / dgrad / wgrad), Cin=1 FFMA kernels, BN/ReLU/pool kernels and the
+ResNet-1D built from them, against plain PyTorch fp32 references."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def _rel(a, b):
+    return float((a.double() - b.double()).norm() / (b.double().norm() + 1e-30))
+
+
+def _bf(t):
+    return t.to(torch.bfloat16).float()
+
+
+CASES = [(4, 500, 16, 16, 5, 2), (2, 360, 64, 128, 7, 3), (3, 130, 256, 256, 3, 1), (2, 500, 32, 48, 31, 15),
+         (5, 127, 128, 64, 1, 0), (1, 300, 768, 256, 7, 3), (2, 64, 16, 16, 3, 0)]
+
+
+@pytest.mark.parametrize("B,L,Cin,Cout,K,pad", CASES)
+def test_conv1d_fwd_dgrad_wgrad(B, L, Cin, Cout, K, pad):
+    from crossscale.ops.conv1d import Conv1dB200
+    torch.manual_seed(B * 100 + K)
+    m = Conv1dB200(Cin, Cout, K, padding=pad, bias=True).to(DEV)
+    with torch.no_grad():
+        m.weight.copy_(_bf(m.weight)); m.bias.copy_(torch.randn(Cout, device=DEV))
+    x = _bf(torch.randn(B, L, Cin, device=DEV)).to(torch.bfloat16).requires_grad_(True)     # channels-last
+    y = m(x)
+    Lout = L + 2 * pad - K + 1
+    assert y.shape == (B, Lout, Cout) and y.dtype == torch.bfloat16
+    xr = x.detach().float().permute(0, 2, 1).contiguous().requires_grad_(True)              # [B,C,L] fp32 oracle
+    wr = m.weight.detach().clone().requires_grad_(True)
+    br = m.bias.detach().clone().requires_grad_(True)
+    yr = F.conv1d(xr, wr, br, padding=pad)
+    assert _rel(y.float().permute(0, 2, 1), yr) < 1e-2
+    dy = _bf(torch.randn(B, Lout, Cout, device=DEV))
+    y.backward(dy.to(torch.bfloat16))
+    yr.backward(dy.permute(0, 2, 1))
+    assert _rel(x.grad.float().permute(0, 2, 1), xr.grad) < 1e-2           # dgrad (bf16 output rounding)
+    assert _rel(m.weight.grad, wr.grad) < 5e-3                              # wgrad (fp32 output)
+    assert _rel(m.bias.grad, br.grad) < 5e-3
+
+
+def test_conv1d_relu_epilogue_and_cin1():
+    from crossscale.ops import _lib
+    from crossscale.ops.conv1d import Conv1dB200, conv1d_fwd_nlc
+    torch.manual_seed(1)
+    x = _bf(torch.randn(2, 200, 32, device=DEV)).to(torch.bfloat16)
+    w = _bf(torch.randn(5, 64, 32, device=DEV) * 0.1).to(torch.bfloat16)
+    bias = torch.randn(64, device=DEV)
+    y = conv1d_fwd_nlc(x, w, bias, 2, relu=True)
+    ref = F.relu(F.conv1d(x.float().permute(0, 2, 1), w.float().permute(1, 2, 0).contiguous(), bias, padding=2))
+    assert _rel(y.float().permute(0, 2, 1), ref) < 1e-2 and float(y.min()) >= 0
+    # first layer: [B,1,L] fp32 -> [B,L,C] bf16, and its weight gradient
+    m = Conv1dB200(1, 64, 7, padding=3, bias=True).to(DEV)
+    xin = torch.randn(6, 1, 500, device=DEV)
+    out = m(xin)
+    wr, br = m.weight.detach().clone().requires_grad_(True), m.bias.detach().clone().requires_grad_(True)
+    ref = F.conv1d(xin, wr, br, padding=3)
+    assert out.shape == (6, 500, 64) and _rel(out.float().permute(0, 2, 1), ref) < 1e-2
+    dy = _bf(torch.randn(6, 500, 64, device=DEV))
+    out.backward(dy.to(torch.bfloat16)); ref.backward(dy.permute(0, 2, 1))
+    assert _rel(m.weight.grad, wr.grad) < 1e-3 and _rel(m.bias.grad, br.grad) < 1e-3
+
+
+@pytest.mark.parametrize("relu,with_res", [(True, False), (True, True), (False, False)])
+def test_bn_relu_residual_kernels(relu, with_res):
+    from crossscale.ops.norm_act import BNReLU1d
+    torch.manual_seed(3)
+    B, L, C = 8, 250, 64
+    bn = BNReLU1d(C, relu=relu).to(DEV)
+    with torch.no_grad():
+        bn.weight.copy_(torch.rand(C, device=DEV) + 0.5); bn.bias.copy_(torch.randn(C, device=DEV) * 0.1)
+    x = _bf(torch.randn(B, L, C, device=DEV) * 2 + 0.3).to(torch.bfloat16).requires_grad_(True)
+    res = _bf(torch.randn(B, L, C, device=DEV)).to(torch.bfloat16).requires_grad_(True) if with_res else None
+    y = bn(x, res)
+    xr = x.detach().float().permute(0, 2, 1).contiguous().requires_grad_(True)
+    rr = res.detach().float().permute(0, 2, 1).contiguous().requires_grad_(True) if with_res else None
+    g, bta = bn.weight.detach().clone().requires_grad_(True), bn.bias.detach().clone().requires_grad_(True)
+    yr = F.batch_norm(xr, None, None, g, bta, True, 0.1, 1e-5)
+    if with_res:
+        yr = yr + rr
+    if relu:
+        yr = F.relu(yr)
+    assert _rel(y.float().permute(0, 2, 1), yr) < 1e-2
+    dy = _bf(torch.randn(B, L, C, device=DEV))
+    y.backward(dy.to(torch.bfloat16)); yr.backward(dy.permute(0, 2, 1))
+    assert _rel(x.grad.float().permute(0, 2, 1), xr.grad) < 3e-2
+    assert _rel(bn.weight.grad, g.grad) < 2e-2 and _rel(bn.bias.grad, bta.grad) < 2e-2
+    if with_res:
+        assert _rel(res.grad.float().permute(0, 2, 1), rr.grad) < 1e-2
+    ref_bn = torch.nn.BatchNorm1d(C).to(DEV)
+    ref_bn(xr.detach())
+    assert _rel(bn.running_mean, ref_bn.running_mean) < 1e-2 and _rel(bn.running_var, ref_bn.running_var) < 1e-2
+
+
+def test_pool_and_layout_kernels():
+    from crossscale.ops import _lib
+    from crossscale.ops.norm_act import global_avg_pool1d
+    x = _bf(torch.randn(5, 123, 48, device=DEV)).to(torch.bfloat16).requires_grad_(True)
+    p = global_avg_pool1d(x)
+    torch.testing.assert_close(p, x.detach().float().mean(1), rtol=1e-4, atol=1e-5)
+    p.backward(torch.ones_like(p))
+    torch.testing.assert_close(x.grad.float(), torch.full_like(x.grad.float(), _bf(torch.tensor(1 / 123)).item()), rtol=1e-2, atol=1e-4)
+    lib = _lib.cuda_lib()
+    a = torch.randn(3, 40, 77, device=DEV)
+    nlc = torch.empty(3, 77, 40, dtype=torch.bfloat16, device=DEV)
+    _lib.check(lib.cs_ncl_f32_to_nlc_bf16(a.data_ptr(), nlc.data_ptr(), 3, 40, 77, _lib.stream_ptr()))
+    torch.testing.assert_close(nlc.float(), _bf(a).permute(0, 2, 1))
+    back = torch.empty_like(a)
+    _lib.check(lib.cs_nlc_bf16_to_ncl_f32(nlc.data_ptr(), back.data_ptr(), 3, 40, 77, _lib.stream_ptr()))
+    torch.testing.assert_close(back, _bf(a))
+
+
+def test_resnet1d_small_matches_cpu_reference():
+    import copy
+    from crossscale.models.resnet1d_wide import resnet1d_small
+    torch.manual_seed(0)
+    cpu = resnet1d_small(5)
+    with torch.no_grad():
+        for p in cpu.parameters():
+            p.copy_(_bf(p))
+    gpu = copy.deepcopy(cpu).to(DEV)
+    x = _bf(torch.randn(16, 1, 360))
+    y = torch.randint(0, 5, (16,))
+    lc = F.cross_entropy(cpu(x), y); lc.backward()
+    lg = F.cross_entropy(gpu(x.to(DEV)), y.to(DEV)); lg.backward()
+    assert abs(float(lc) - float(lg)) < 3e-2
+    num = den = 0.0
+    for (n, a), b in zip(cpu.named_parameters(), gpu.parameters()):
+        num += float((a.grad - b.grad.cpu()).double().pow(2).sum()); den += float(a.grad.double().pow(2).sum())
+    assert (num / den) ** 0.5 < 0.1          # whole-gradient relative error through 5 bf16 conv layers + BN
