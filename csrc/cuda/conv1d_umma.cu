@@ -66,7 +66,9 @@ __device__ __forceinline__ void tma_load_4d(void* dst, const CUtensorMap* map, u
 
 // ------------------------------------------------------------------------------------------------
 // K1 forward (dgrad reuses it with flipped / transposed weights)
-// CTA = (n tile, 128-position tile, sample).  192 threads: warp 0 TMA, warp 1 MMA, warps 2-5 epilogue.
+// CTA = (n tile, group of MT 128-position tiles, sample).  192 threads: warp 0 TMA, warp 1 MMA, warps 2-5
+// epilogue.  Every weight stage (one tap of one 64-channel chunk) is reused by all MT position tiles, which
+// cuts the L2->SM weight traffic per FLOP by MT (the single-tile version is L2-bandwidth bound at C = 256).
 // ------------------------------------------------------------------------------------------------
 constexpr int kFwdThreads = 192;
 constexpr int kAStages = 2, kWStages = 4;
@@ -76,6 +78,7 @@ struct FwdShape {
     int CK;          // channels per reduction chunk (16 / 32 / 64)
     int NT;          // output channels per CTA (16 .. 128)
     int R;           // rows per activation tile = 128 + K - 1
+    int MT;          // 128-position tiles per CTA (1, 2 or 4): weights are streamed once for all of them
 };
 
 __global__ void __launch_bounds__(kFwdThreads, 1)
@@ -83,18 +86,21 @@ conv1d_fwd_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
                   const float* __restrict__ bias, __nv_bfloat16* __restrict__ y, FwdShape s) {
     extern __shared__ __align__(128) uint8_t smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int n0 = blockIdx.x * s.NT, l0 = blockIdx.y * 128, b = blockIdx.z;
-    const int a_bytes = s.R * 16 * (s.CK / 8);              // one activation chunk: CK/8 planes of R rows
+    const int n0 = blockIdx.x * s.NT, l0 = blockIdx.y * 128 * s.MT, b = blockIdx.z;
+    const int a_tile = s.R * 16 * (s.CK / 8);               // one position tile of a chunk: CK/8 planes of R rows
+    const int a_tile_stride = (a_tile + 127) & ~127;
+    const int a_bytes = a_tile_stride * s.MT;               // ring slot: MT tiles
     const int w_bytes = s.NT * 16 * (s.CK / 8);             // one tap of weights for that chunk
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem);
     uint64_t* full_a = bars, *empty_a = bars + kAStages, *full_w = bars + 2 * kAStages, *empty_w = full_w + kWStages;
     uint64_t* acc_full = empty_w + kWStages;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_full + 1);
     uint8_t* a_ring = smem + 256;
-    uint8_t* w_ring = a_ring + kAStages * ((a_bytes + 127) & ~127);
-    const int a_stride = (a_bytes + 127) & ~127, w_stride = (w_bytes + 127) & ~127;
+    uint8_t* w_ring = a_ring + kAStages * a_bytes;
+    const int a_stride = a_bytes, w_stride = (w_bytes + 127) & ~127;
     const int chunks = s.Cin / s.CK;
-    const uint32_t tmem_cols = s.NT <= 32 ? 32 : (s.NT <= 64 ? 64 : 128);
+    uint32_t tmem_cols = 32;
+    while ((int)tmem_cols < s.NT * s.MT) tmem_cols <<= 1;
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < kAStages; ++i) { mbar_init(full_a + i, 1); mbar_init(empty_a + i, 1); }
@@ -116,8 +122,10 @@ conv1d_fwd_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
             for (int c = 0; c < chunks; ++c) {
                 const int sa = c % kAStages;
                 if (c >= kAStages) mbar_wait(empty_a + sa, ((c / kAStages) - 1) & 1);
-                mbar_arrive_expect_tx(full_a + sa, a_bytes);
-                tma_load_4d(a_ring + sa * a_stride, &map_x, full_a + sa, 0, l0 - s.pad, c * (s.CK / 8), b);
+                mbar_arrive_expect_tx(full_a + sa, a_tile * s.MT);
+                for (int i = 0; i < s.MT; ++i)
+                    tma_load_4d(a_ring + sa * a_stride + i * a_tile_stride, &map_x, full_a + sa, 0, l0 + i * 128 - s.pad,
+                                c * (s.CK / 8), b);
                 for (int k = 0; k < s.K; ++k, ++wi) {
                     const int sw = wi % kWStages;
                     if (wi >= kWStages) mbar_wait(empty_w + sw, ((wi / kWStages) - 1) & 1);
@@ -145,10 +153,12 @@ conv1d_fwd_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
                     const uint64_t b0 = smem_desc(smem_u32(w_ring + sw * w_stride), plane_w, 128);
                     for (int j = 0; j < s.CK / 16; ++j) {
                         // 16 channels = planes 2j, 2j+1; tap k = k rows further down the tile
-                        mma_f16(tmem_base, a0 + (uint64_t)((2 * j * plane_a) >> 4) + (uint64_t)k,
-                                b0 + (uint64_t)((2 * j * plane_w) >> 4), idesc, first ? 0u : 1u);
-                        first = 0;
+                        const uint64_t bj = b0 + (uint64_t)((2 * j * plane_w) >> 4);
+                        for (int i = 0; i < s.MT; ++i)
+                            mma_f16(tmem_base + i * s.NT, a0 + (uint64_t)((i * a_tile_stride + 2 * j * plane_a) >> 4) + (uint64_t)k,
+                                    bj, idesc, (first && j == 0) ? 0u : 1u);
                     }
+                    first = 0;
                     mma_commit(empty_w + sw);            // weights slot free once these MMAs retire
                 }
                 mma_commit(empty_a + sa);
@@ -160,11 +170,12 @@ conv1d_fwd_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
         const int q = warp & 3;                           // TMEM sub-partition of this warp (warp id mod 4)
         mbar_wait(acc_full, 0);
         tc_fence_after_sync();
-        const int l = l0 + q * 32 + lane;
+        for (int i = 0; i < s.MT; ++i) {
+        const int l = l0 + i * 128 + q * 32 + lane;
         __nv_bfloat16* dst = y + ((size_t)b * s.Lout + l) * s.Cout + n0;
         for (int c0 = 0; c0 < s.NT; c0 += 16) {
             uint32_t v[16];
-            tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + c0, v);
+            tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + i * s.NT + c0, v);
             tmem_ld_wait();
             if (l < s.Lout) {
                 uint32_t pk[8];
@@ -180,6 +191,7 @@ conv1d_fwd_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
                 d4[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
                 d4[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
             }
+        }
         }
     }
     tc_fence_before_sync();
@@ -206,8 +218,14 @@ int conv1d_fwd(const void* x, const void* w, const float* bias, void* y, int B, 
     if (rc) return rc;
     rc = make_plane_map(&mw, w, K, Cout, Cin, s.NT, s.CK / 8);
     if (rc) return rc;
-    const int a_bytes = s.R * 16 * (s.CK / 8), w_bytes = s.NT * 16 * (s.CK / 8);
-    const size_t smem = 256 + (size_t)kAStages * ((a_bytes + 127) & ~127) + (size_t)kWStages * ((w_bytes + 127) & ~127);
+    const int tiles = (s.Lout + 127) / 128;
+    s.MT = tiles >= 4 ? 4 : tiles;                          // TMEM: MT * NT <= 512 columns
+    const int a_tile = (s.R * 16 * (s.CK / 8) + 127) & ~127, w_bytes = s.NT * 16 * (s.CK / 8);
+    size_t smem = 256 + (size_t)kAStages * a_tile * s.MT + (size_t)kWStages * ((w_bytes + 127) & ~127);
+    while (smem > 220 * 1024 && s.MT > 1) {                 // very wide taps: fewer tiles per CTA
+        s.MT >>= 1;
+        smem = 256 + (size_t)kAStages * a_tile * s.MT + (size_t)kWStages * ((w_bytes + 127) & ~127);
+    }
     static size_t configured[64] = {};
     int dev = 0;
     CS_CUDA_OK(cudaGetDevice(&dev));
@@ -215,7 +233,7 @@ int conv1d_fwd(const void* x, const void* w, const float* bias, void* y, int B, 
         CS_CUDA_OK(cudaFuncSetAttribute(conv1d_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured[dev & 63] = smem;
     }
-    dim3 grid(Cout / s.NT, (s.Lout + 127) / 128, B);
+    dim3 grid(Cout / s.NT, (tiles + s.MT - 1) / s.MT, B);
     conv1d_fwd_kernel<<<grid, kFwdThreads, smem, st>>>(mx, mw, bias, (__nv_bfloat16*)y, s);
     CS_CUDA_OK(cudaGetLastError());
     return CS_OK;
