@@ -125,6 +125,84 @@ class TorchLocalTrainer:
         return loss_acc, n
 
 
+class _ScaledCE(torch.autograd.Function):
+    """mean cross entropy with the loss scale folded into the gradient (K5 kernel)."""
+
+    @staticmethod
+    def forward(ctx, logits, y, scale_t):
+        from ..ops import _lib
+        logits = logits.float().contiguous()
+        b, c = logits.shape
+        loss = torch.empty(1, dtype=torch.float32, device=logits.device)
+        dl = torch.empty_like(logits)
+        _lib.check(_lib.cuda_lib().cs_cross_entropy_fwd_bwd(logits.data_ptr(), y.data_ptr(), b, c, _lib.ptr(scale_t),
+                                                            loss.data_ptr(), dl.data_ptr(), _lib.stream_ptr()), "cs_cross_entropy")
+        ctx.save_for_backward(dl)
+        return loss[0]
+
+    @staticmethod
+    def backward(ctx, g):
+        (dl,) = ctx.saved_tensors
+        return dl * g, None, None
+
+
+class KernelLocalTrainer:
+    """Any model built from this package's ops (e.g. ResNet-1D wide) on CUDA: autograd drives the
+    tcgen05 conv / BN kernels, the loss is the CE kernel, the update is ONE flat SGD-momentum kernel
+    over the parameter arena (found-inf aware when the fp16-style scaler is on), and with
+    ``sync_grads`` the gradient buckets are all-reduced in-kernel over NVLink while backward runs."""
+
+    def __init__(self, model: torch.nn.Module, device, lr=1e-2, momentum=0.9, use_scaler: bool = False,
+                 sync_grads: bool = False, bucket_bytes: int = 4 << 20, wire: str = "fp32"):
+        from ..models.tiny_ecg import FlatParams
+        from ..ops import _lib
+        self.model, self.device, self._lib = model, torch.device(device), _lib
+        self.flat = FlatParams(model, align=4)
+        self.lr, self.momentum, self.use_scaler = float(lr), float(momentum), bool(use_scaler)
+        self.mom = torch.zeros_like(self.flat.flat)
+        self.ctrl = torch.zeros(8, dtype=torch.int32, device=self.device)
+        self.fstate = torch.zeros(8, dtype=torch.float32, device=self.device)
+        self.fstate[tk.FS_SCALE] = 65536.0 if use_scaler else 1.0
+        self.loss_sum = torch.zeros((), dtype=torch.float32, device=self.device)
+        self.sync = None
+        if sync_grads:
+            from ..parallel.grad_sync import GradSync
+            self.sync = GradSync(self.flat, bucket_bytes=bucket_bytes, wire=wire)
+        self.launches = 0
+
+    def flat_parameters(self) -> torch.Tensor:
+        return self.flat.flat
+
+    def load_flat(self, flat: torch.Tensor) -> None:
+        if flat.data_ptr() != self.flat.flat.data_ptr():
+            self.flat.flat.copy_(flat)
+
+    def step(self, x, y) -> torch.Tensor:
+        self.model.train()
+        self.flat.grad.zero_()
+        loss = _ScaledCE.apply(self.model(x), y, self.fstate[tk.FS_SCALE:tk.FS_SCALE + 1] if self.use_scaler else None)
+        loss.backward()
+        if self.sync is not None:
+            self.sync.finish()
+        n = self.flat.flat.numel()
+        self._lib.check(self._lib.cuda_lib().cs_sgd_momentum(
+            self.flat.flat.data_ptr(), self.mom.data_ptr(), self.flat.grad.data_ptr(), n, self.lr, self.momentum, 0.0,
+            int(self.use_scaler), self.ctrl.data_ptr(), self.fstate.data_ptr(), 2.0, 0.5, 2000, None,
+            self._lib.stream_ptr()), "cs_sgd_momentum")
+        self.launches += 1
+        self.loss_sum += loss.detach()
+        return loss.detach()
+
+    def run_steps(self, batch_iter: Iterator, steps: int) -> Tuple[float, int]:
+        n = 0
+        self.loss_sum.zero_()
+        for _ in range(steps):
+            x, y = next(batch_iter)
+            n += x.size(0)
+            self.step(x, y)
+        return float(self.loss_sum.item()), n
+
+
 class FusedTinyTrainer:
     """TinyECG local training with the one-launch step kernel + CUDA-graph replay."""
 
@@ -238,7 +316,8 @@ class FedAvgRunner:
                  rank: int = 0, world: int = 1, lr: float = 1e-2, momentum: float = 0.9,
                  agg_backend: str = "auto", wire: str = "fp32", server_lr: float = 1.0,
                  reset_momentum: bool = False, use_graph: bool = True,
-                 generator: Optional[torch.Generator] = None, model_name: str = "tiny_ecg"):
+                 generator: Optional[torch.Generator] = None, model_name: str = "tiny_ecg",
+                 sync_grads: bool = False):
         self.device = torch.device(device)
         self.model, self.rank, self.world = model, rank, world
         self.batch, self.local_steps, self.config = batch_size, local_steps, config
@@ -256,12 +335,18 @@ class FedAvgRunner:
             self.batch_iter = None
         else:
             from ..data.shard_dataset import make_gpu_batch_iter
-            self.trainer = TorchLocalTrainer(model, self.device, lr, momentum,
-                                             amp if self.device.type == "cuda" else "none")
+            self.kernel_generic = (self.device.type == "cuda" and tk.use_kernels() and not isinstance(model, TinyECG))
+            if self.kernel_generic:
+                self.trainer = KernelLocalTrainer(model, self.device, lr, momentum, use_scaler=(amp == "fp16"),
+                                                  sync_grads=sync_grads)
+                self.mom = self.trainer.mom
+            else:
+                self.trainer = TorchLocalTrainer(model, self.device, lr, momentum,
+                                                 amp if self.device.type == "cuda" else "none")
+                self.mom = None
             self.batch_iter = make_gpu_batch_iter(x_gpu, y_gpu, batch_size, generator)
             self.flat = self.trainer.flat_parameters()
             self.numel = self.flat.numel()
-            self.mom = None
         self.weight = client_weight(x_gpu.shape[0], self.device)
         broadcast_model(self.flat)                       # round 0: common initial model
         if not self.fused:
@@ -286,7 +371,7 @@ class FedAvgRunner:
             self.trainer.run_round_resident()
         else:
             loss_acc, n_samples = self.trainer.run_steps(self.batch_iter, self.local_steps)
-            self.flat = self.trainer.flat_parameters()
+            self.flat = self.trainer.flat_parameters()   # (a view of the arena for the kernel trainer)
         t1 = time.perf_counter()
         if cuda:
             e1.record()

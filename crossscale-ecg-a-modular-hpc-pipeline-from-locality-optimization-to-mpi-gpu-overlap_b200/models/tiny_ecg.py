@@ -58,32 +58,34 @@ def num_params(num_classes: int) -> int:
 class FlatParams:
     """Re-homes a module's parameters (and their grads) as views of flat fp32 buffers."""
 
-    def __init__(self, module: nn.Module, pad_to: int = 4):
+    def __init__(self, module: nn.Module, pad_to: int = 4, align: int = 1):
+        """``align`` > 1 starts every parameter at a multiple of ``align`` floats (16-byte aligned slices for
+        bucketed collectives); the default packs densely — the layout the fused TinyECG kernels index."""
         params = list(module.parameters())
-        total = sum(p.numel() for p in params)
+        self.offsets: List[int] = []
+        total = 0
+        for p in params:
+            total = (total + align - 1) // align * align
+            self.offsets.append(total)
+            total += p.numel()
         padded = (total + pad_to - 1) // pad_to * pad_to
         dev = params[0].device if params else torch.device("cpu")
         self.numel = total
         self.flat = torch.zeros(padded, dtype=torch.float32, device=dev)
         self.grad = torch.zeros(padded, dtype=torch.float32, device=dev)
-        off = 0
-        for p in params:
+        for p, off in zip(params, self.offsets):
             n = p.numel()
             self.flat[off:off + n].copy_(p.data.reshape(-1).float())
             p.data = self.flat[off:off + n].view_as(p)
             p.grad = self.grad[off:off + n].view_as(p)
-            off += n
         self.params = params
 
     def rebind(self, new_flat: torch.Tensor) -> None:
         """Point every parameter at ``new_flat`` (e.g. a symmetric-memory arena)."""
         new_flat[: self.flat.numel()].copy_(self.flat)
         self.flat = new_flat
-        off = 0
-        for p in self.params:
-            n = p.numel()
-            p.data = new_flat[off:off + n].view_as(p)
-            off += n
+        for p, off in zip(self.params, self.offsets):
+            p.data = new_flat[off:off + p.numel()].view_as(p)
 
 
 class TinyECG(nn.Module):

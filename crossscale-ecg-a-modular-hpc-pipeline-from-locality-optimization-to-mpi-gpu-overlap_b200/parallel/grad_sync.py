@@ -1,0 +1,101 @@
+"""K8: bucketed gradient all-reduce overlapped with backward (north-star extension; the reference has no
+intra-round gradient exchange).
+
+The model's gradients live in one flat fp32 arena (``models.tiny_ecg.FlatParams``); a bucket is a
+contiguous slice of it.  A post-accumulate-grad hook counts the parameters of each bucket; when the
+last one arrives the bucket's all-reduce is enqueued on a SIDE stream (after an event on the compute
+stream), so the collective of bucket *i* runs while autograd is still producing bucket *i+1*.  Each
+in-flight bucket has its own barrier channel and arena region.  The collective itself is the in-kernel
+NVLink two-shot of ``csrc/cuda/fedavg.cu`` (``cs_allreduce_bucket``) — no NCCL on this path.
+``finish()`` makes the compute stream wait for every bucket before the optimizer step.
+"""
+from __future__ import annotations
+
+from typing import List, Optional
+
+import torch
+import torch.distributed as dist
+
+from ..models.tiny_ecg import FlatParams
+from ..ops import _lib
+from .symm import SymmetricComm
+
+MAX_CHANNELS = 8
+
+
+class GradSync:
+    def __init__(self, flat: FlatParams, bucket_bytes: int = 4 << 20, wire: str = "fp32",
+                 comm: Optional[SymmetricComm] = None, backend: str = "kernel"):
+        self.flat, self.wire_bf16 = flat, int(wire == "bf16")
+        self.world = dist.get_world_size() if dist.is_initialized() else 1
+        self.backend = backend if self.world > 1 or backend == "kernel" else "none"
+        dev = flat.flat.device
+        # buckets in REVERSE parameter order (gradients arrive roughly last layer first); the arena must have been
+        # built with ``align=4`` so every bucket boundary is 16-byte aligned and buckets are disjoint
+        if any(o % 4 for o in flat.offsets):
+            raise ValueError("GradSync needs FlatParams(model, align=4)")
+        self.buckets: List[dict] = []
+        hi = (flat.numel + 3) // 4 * 4
+        cur, members = 0, []
+        for i in reversed(range(len(flat.params))):
+            members.append(i)
+            cur += flat.params[i].numel() * 4
+            if cur >= bucket_bytes or i == 0:
+                self.buckets.append({"lo_al": flat.offsets[i], "hi_al": hi, "members": list(members), "pending": len(members)})
+                hi, cur, members = flat.offsets[i], 0, []
+        lib = _lib.cuda_lib()
+        self.channels = min(MAX_CHANNELS, max(1, len(self.buckets)))
+        self.region = max(int(lib.cs_fedavg_arena_bytes(b["hi_al"] - b["lo_al"], self.wire_bf16, self.world)) for b in self.buckets)
+        self.region = (self.region + 255) // 256 * 256
+        self.comm = comm
+        if self.backend == "kernel":
+            need = self.region * self.channels
+            if self.comm is None:
+                self.comm = SymmetricComm(need)
+            elif self.comm.arena_bytes < need:
+                raise ValueError("grad-sync arena too small")
+        self.streams = [torch.cuda.Stream(device=dev) for _ in range(self.channels)]
+        self.done_events = [torch.cuda.Event() for _ in self.buckets]
+        self.launches = 0
+        self._owner = {}
+        for j, b in enumerate(self.buckets):
+            for i in b["members"]:
+                self._owner[i] = j
+        for i, p in enumerate(flat.params):
+            p.register_post_accumulate_grad_hook(self._make_hook(i))
+
+    def _make_hook(self, i: int):
+        def hook(_p):
+            j = self._owner[i]
+            b = self.buckets[j]
+            b["pending"] -= 1
+            if b["pending"] == 0:
+                self._launch(j)
+        return hook
+
+    def _launch(self, j: int) -> None:
+        b = self.buckets[j]
+        ch = j % self.channels
+        side = self.streams[ch]
+        ready = torch.cuda.Event()
+        ready.record()                                     # gradients of this bucket are complete on the compute stream
+        side.wait_event(ready)
+        g = self.flat.grad[b["lo_al"]:b["hi_al"]]
+        n = b["hi_al"] - b["lo_al"]
+        if self.backend == "kernel":
+            _lib.check(_lib.cuda_lib().cs_allreduce_bucket(self.comm.handle, g.data_ptr(), n, 1.0 / self.world, self.wire_bf16,
+                                                           ch * self.region, ch, side.cuda_stream), "cs_allreduce_bucket")
+        elif self.backend == "nccl" and self.world > 1:
+            with torch.cuda.stream(side):
+                dist.all_reduce(g)
+                g.mul_(1.0 / self.world)
+        self.done_events[j].record(side)
+        self.launches += 1
+
+    def finish(self) -> None:
+        """Compute stream waits for every bucket; re-arms the hooks for the next backward."""
+        cur = torch.cuda.current_stream()
+        for j, b in enumerate(self.buckets):
+            if b["pending"] == 0:
+                cur.wait_event(self.done_events[j])
+            b["pending"] = len(b["members"])
