@@ -38,6 +38,8 @@ def build_parser() -> argparse.ArgumentParser:
     ap.add_argument("--server-lr", type=float, default=1.0)
     ap.add_argument("--reset-momentum", action="store_true")
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--sync-grads", action="store_true",
+                    help="all-reduce gradients every step (bucketed, overlapped with backward) in addition to FedAvg")
     ap.add_argument("--results-dir", type=str, default="results")
     ap.add_argument("--save", type=str, default=None, help="save the final global state_dict here")
     ap.add_argument("--load", type=str, default=None, help="start from this state_dict")
@@ -66,7 +68,7 @@ def main(argv=None):
                               amp=("none" if cfg == "G0" else args.amp), rank=rank, world=world,
                               agg_backend=args.agg_backend, wire=args.wire, server_lr=args.server_lr,
                               reset_momentum=args.reset_momentum, use_graph=not args.no_graph,
-                              model_name=args.model)
+                              model_name=args.model, sync_grads=args.sync_grads)
         rows = runner.run(args.rounds)
         gathered = launch.gather_rows(rows)
         if rank == 0:

@@ -24,7 +24,7 @@ namespace cs {
 
 constexpr int kMaxRanks = CS_MAX_RANKS;
 constexpr int kChannels = 8;          // independent barrier channels (streams / buckets in flight)
-constexpr int kMaxBlocks = 128;       // blocks per collective kernel (all must be co-resident)
+constexpr int kMaxBlocks = 160;       // blocks per collective kernel (a block only ever waits for the same block on peers)
 constexpr int kCommThreads = 512;
 constexpr size_t kSignalWords = (size_t)kChannels * kMaxBlocks * kMaxRanks;
 constexpr int64_t kOneShotMaxElems = 64 * 1024;   // 256 KiB of fp32
@@ -165,102 +165,146 @@ __global__ void __launch_bounds__(kCommThreads) fedavg_oneshot_kernel(const Comm
 }
 
 // ------------------------------------------------------------------------------------------------
-// two-shot: IN region [P ranks' own data is local only][n], OUT region [n]; both in every arena.
-// Arena layout at arena_off: IN[n] then OUT[n] (wire elements, 16-byte aligned).
-// Element i belongs to slice s = owner rank, and inside a slice to block b: the partition is the
-// same on every rank, so block b only ever consumes what peer blocks b produced (per-block flags).
+// two-shot.  Arena layout at arena_off: IN[n] then OUT[n] (wire elements).  The vector is cut into groups
+// of 4 elements; slice s (owner rank s) and, inside a slice, block b get fixed group ranges — the same on
+// every rank — so block b only ever consumes what peer blocks b produced (per-block flags suffice and no
+// block waits for another block of its own GPU).  Every loop issues kU independent 16-byte loads per
+// thread before the first use: ~5 MB in flight per GPU, enough to cover HBM and NVLink latency.
 // ------------------------------------------------------------------------------------------------
+constexpr int kU = 4;
+
+template <bool BF16> struct Wire4;
+template <> struct Wire4<false> {
+    static constexpr int BYTES = 16;
+    __device__ static void st(char* base, long long g, float4 v) { reinterpret_cast<float4*>(base)[g] = v; }
+    __device__ static float4 ld(const char* base, long long g) { return __ldcg(reinterpret_cast<const float4*>(base) + g); }
+};
+template <> struct Wire4<true> {
+    static constexpr int BYTES = 8;
+    __device__ static void st(char* base, long long g, float4 v) {
+        __nv_bfloat162 a = __floats2bfloat162_rn(v.x, v.y), b = __floats2bfloat162_rn(v.z, v.w);
+        reinterpret_cast<uint2*>(base)[g] = make_uint2(*reinterpret_cast<uint32_t*>(&a), *reinterpret_cast<uint32_t*>(&b));
+    }
+    __device__ static float4 ld(const char* base, long long g) {
+        const uint2 r = __ldcg(reinterpret_cast<const uint2*>(base) + g);
+        const float2 a = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&r.x));
+        const float2 b = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&r.y));
+        return make_float4(a.x, a.y, b.x, b.y);
+    }
+};
+
+// 4 floats of a possibly ragged fp32 vector (the last group may be partial)
+__device__ __forceinline__ float4 ld4_tail(const float* p, long long g, long long n) {
+    if (4 * g + 3 < n) return *reinterpret_cast<const float4*>(p + 4 * g);
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (4 * g < n) v.x = p[4 * g];
+    if (4 * g + 1 < n) v.y = p[4 * g + 1];
+    if (4 * g + 2 < n) v.z = p[4 * g + 2];
+    return v;
+}
+__device__ __forceinline__ void st4_tail(float* p, long long g, long long n, float4 v) {
+    if (4 * g + 3 < n) { *reinterpret_cast<float4*>(p + 4 * g) = v; return; }
+    if (4 * g < n) p[4 * g] = v.x;
+    if (4 * g + 1 < n) p[4 * g + 1] = v.y;
+    if (4 * g + 2 < n) p[4 * g + 2] = v.z;
+}
+
 template <bool BF16>
 __global__ void __launch_bounds__(kCommThreads) fedavg_twoshot_kernel(const CommDev* ctxs, AggCall a) {
-    using W = Wire<BF16>;
-    using T = typename W::T;
-    constexpr int V = 16 / sizeof(T);            // elements per 16-byte vector
+    using W = Wire4<BF16>;
     const int er = blockIdx.y;
     const CommDev& c = ctxs[er];
-    const int P = c.world, b = blockIdx.x, nb = gridDim.x;
+    const int P = c.world, b = blockIdx.x, nb = gridDim.x, T = blockDim.x, tid = threadIdx.x;
     uint32_t* ep = c.epochs + (size_t)a.channel * kMaxBlocks + b;
     const uint32_t e0 = *ep;
     const long long n = a.n;
     float* local = a.local[er];
-    const float* prev = a.prev[er];
+    float* prev = a.prev[er];
+    float* mom = a.mom[er];
     const float w = a.weight[er];
-    const size_t region = (size_t)((n + 63) & ~63ll);
-    // vectors: nv = ceil(n / V); slice s covers vectors [s*vps, (s+1)*vps); block b a sub-range of it
-    const long long nv = (n + V - 1) / V;
-    const long long vps = (nv + P - 1) / P;                  // vectors per slice
-    const long long vpb = (vps + nb - 1) / nb;               // vectors per (slice, block)
+    const long long n4 = (n + 3) >> 2;                       // groups of 4 elements
+    const long long gps = (n4 + P - 1) / P;                  // groups per slice
+    const long long gpb = (gps + nb - 1) / nb;               // groups per (slice, block)
+    const size_t region = (size_t)((n4 * W::BYTES + 255) & ~255ll);   // bytes of IN (OUT follows)
+    char* my_in = c.arena[c.rank] + a.arena_off;
+    const char* my_out = my_in + region;
 
-    T* my_in = reinterpret_cast<T*>(c.arena[c.rank] + a.arena_off);
-    // phase 1: IN = enc(w * (local - prev)) for the (slice, block) pieces this block owns
+    // phase 1: IN = enc(w * (local - prev)) for every (slice, this block) piece
     for (int s = 0; s < P; ++s) {
-        const long long v0 = s * vps + (long long)b * vpb;
-        long long v1 = v0 + vpb; if (v1 > (s + 1) * vps) v1 = (s + 1) * vps; if (v1 > nv) v1 = nv;
-        for (long long v = v0 + threadIdx.x; v < v1; v += blockDim.x) {
-            T tmp[V];
+        const long long g0 = s * gps + (long long)b * gpb;
+        long long g1 = g0 + gpb; if (g1 > (s + 1) * gps) g1 = (s + 1) * gps; if (g1 > n4) g1 = n4;
+        for (long long g = g0 + tid; g < g1; g += (long long)kU * T) {
+            float4 x[kU], q[kU];
 #pragma unroll
-            for (int j = 0; j < V; ++j) {
-                const long long i = v * V + j;
-                float x = 0.0f;
-                if (i < n) x = w * (prev ? local[i] - prev[i] : local[i]);
-                tmp[j] = W::enc(x);
+            for (int u = 0; u < kU; ++u) {
+                const long long gi = g + (long long)u * T;
+                if (gi < g1) { x[u] = ld4_tail(local, gi, n); if (prev) q[u] = ld4_tail(prev, gi, n); }
             }
-            *reinterpret_cast<uint4*>(my_in + v * V) = *reinterpret_cast<const uint4*>(tmp);
+#pragma unroll
+            for (int u = 0; u < kU; ++u) {
+                const long long gi = g + (long long)u * T;
+                if (gi < g1) {
+                    float4 v = x[u];
+                    if (prev) { v.x -= q[u].x; v.y -= q[u].y; v.z -= q[u].z; v.w -= q[u].w; }
+                    W::st(my_in, gi, make_float4(w * v.x, w * v.y, w * v.z, w * v.w));
+                }
+            }
         }
     }
     xgpu_barrier(c, a.channel, b, e0 + 1);
-    // phase 2: reduce my slice from every peer's IN (P2P loads), push the result to every OUT
+    // phase 2: reduce my slice from every peer's IN (P2P loads), push the result into every peer's OUT
     {
         const int s = c.rank;
-        const long long v0 = s * vps + (long long)b * vpb;
-        long long v1 = v0 + vpb; if (v1 > (s + 1) * vps) v1 = (s + 1) * vps; if (v1 > nv) v1 = nv;
-        for (long long v = v0 + threadIdx.x; v < v1; v += blockDim.x) {
-            float acc[V];
+        const long long g0 = s * gps + (long long)b * gpb;
+        long long g1 = g0 + gpb; if (g1 > (s + 1) * gps) g1 = (s + 1) * gps; if (g1 > n4) g1 = n4;
+        constexpr int U2 = 2;
+        for (long long g = g0 + tid; g < g1; g += (long long)U2 * T) {
+            float4 r[U2][kMaxRanks];
 #pragma unroll
-            for (int j = 0; j < V; ++j) acc[j] = 0.0f;
-            uint4 raw[kMaxRanks];
+            for (int u = 0; u < U2; ++u) {
+                const long long gi = g + (long long)u * T;
 #pragma unroll
-            for (int r = 0; r < kMaxRanks; ++r) {
-                if (r < P) {
-                    const T* src = reinterpret_cast<const T*>(c.arena[(c.rank + r) % P] + a.arena_off);
-                    raw[r] = __ldcg(reinterpret_cast<const uint4*>(src + v * V));
-                }
+                for (int p = 0; p < kMaxRanks; ++p)
+                    if (p < P && gi < g1) r[u][p] = W::ld(c.arena[(c.rank + p) % P] + a.arena_off, gi);
             }
 #pragma unroll
-            for (int r = 0; r < kMaxRanks; ++r) {
-                if (r < P) {
-                    const T* t = reinterpret_cast<const T*>(&raw[r]);
+            for (int u = 0; u < U2; ++u) {
+                const long long gi = g + (long long)u * T;
+                if (gi < g1) {
+                    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-                    for (int j = 0; j < V; ++j) acc[j] += W::dec(t[j]);
+                    for (int p = 0; p < kMaxRanks; ++p)
+                        if (p < P) { acc.x += r[u][p].x; acc.y += r[u][p].y; acc.z += r[u][p].z; acc.w += r[u][p].w; }
+                    acc.x *= a.post_scale; acc.y *= a.post_scale; acc.z *= a.post_scale; acc.w *= a.post_scale;
+                    for (int p = 0; p < P; ++p) W::st(c.arena[(c.rank + p) % P] + a.arena_off + region, gi, acc);
                 }
-            }
-            T outv[V];
-#pragma unroll
-            for (int j = 0; j < V; ++j) outv[j] = W::enc(acc[j] * a.post_scale);
-            const uint4 packed = *reinterpret_cast<const uint4*>(outv);
-            for (int r = 0; r < P; ++r) {
-                T* dst = reinterpret_cast<T*>(c.arena[(c.rank + r) % P] + a.arena_off) + region;
-                *reinterpret_cast<uint4*>(dst + v * V) = packed;
             }
         }
     }
     xgpu_barrier(c, a.channel, b, e0 + 2);
     // phase 3: local server update from OUT
-    const T* my_out = reinterpret_cast<const T*>(c.arena[c.rank] + a.arena_off) + region;
     for (int s = 0; s < P; ++s) {
-        const long long v0 = s * vps + (long long)b * vpb;
-        long long v1 = v0 + vpb; if (v1 > (s + 1) * vps) v1 = (s + 1) * vps; if (v1 > nv) v1 = nv;
-        for (long long v = v0 + threadIdx.x; v < v1; v += blockDim.x) {
-            const uint4 raw = __ldcg(reinterpret_cast<const uint4*>(my_out + v * V));
-            const T* t = reinterpret_cast<const T*>(&raw);
+        const long long g0 = s * gps + (long long)b * gpb;
+        long long g1 = g0 + gpb; if (g1 > (s + 1) * gps) g1 = (s + 1) * gps; if (g1 > n4) g1 = n4;
+        for (long long g = g0 + tid; g < g1; g += (long long)kU * T) {
+            float4 d[kU], q[kU];
 #pragma unroll
-            for (int j = 0; j < V; ++j) {
-                const long long i = v * V + j;
-                if (i < n) {
-                    const float d = W::dec(t[j]);
-                    const float out = prev ? prev[i] + a.server_lr * d : d;
-                    local[i] = out;
-                    if (prev) a.prev[er][i] = out;
-                    if (a.mom[er]) a.mom[er][i] = 0.0f;
+            for (int u = 0; u < kU; ++u) {
+                const long long gi = g + (long long)u * T;
+                if (gi < g1) { d[u] = W::ld(my_out, gi); if (prev) q[u] = ld4_tail(prev, gi, n); }
+            }
+#pragma unroll
+            for (int u = 0; u < kU; ++u) {
+                const long long gi = g + (long long)u * T;
+                if (gi < g1) {
+                    float4 o = d[u];
+                    if (prev) {
+                        o = make_float4(q[u].x + a.server_lr * o.x, q[u].y + a.server_lr * o.y, q[u].z + a.server_lr * o.z,
+                                        q[u].w + a.server_lr * o.w);
+                        st4_tail(prev, gi, n, o);
+                    }
+                    st4_tail(local, gi, n, o);
+                    if (mom) st4_tail(mom, gi, n, make_float4(0.f, 0.f, 0.f, 0.f));
                 }
             }
         }
@@ -386,14 +430,14 @@ int comm_destroy(cs_comm* c) {
 static int pick_blocks(long long n, bool oneshot) {
     if (oneshot) { long long b = (n + 4095) / 4096; return (int)(b < 1 ? 1 : (b > 16 ? 16 : b)); }
     int cap = num_sms() < kMaxBlocks ? num_sms() : kMaxBlocks;
-    long long b = (n + 16383) / 16384;
+    long long b = (n + 8191) / 8192;
     return (int)(b < 1 ? 1 : (b > cap ? cap : b));
 }
 
 size_t agg_arena_need(long long n, int wire_bf16, int world) {
     const size_t es = wire_bf16 ? 2 : 4;
     if (n <= kOneShotMaxElems) return 2 * (size_t)world * (size_t)((n + 7) & ~7ll) * es;
-    return 2 * (size_t)((n + 63) & ~63ll) * es;
+    return 2 * (size_t)(((((n + 3) >> 2) * (es * 4)) + 255) & ~255ll);
 }
 
 // Launch for a real rank (ranks = 1 context) or for an emulated group (ranks = world contexts).
@@ -406,15 +450,17 @@ static int launch_agg(const CommDev* ctxs, int ranks, int world, size_t arena_by
                agg_arena_need(a.n, a.wire_bf16, world), a.arena_off, arena_bytes);
     const bool oneshot = a.n <= kOneShotMaxElems;
     int nb = pick_blocks(a.n, oneshot);
-    if (ranks > 1) {   // emulated ranks share one GPU: keep the whole grid co-resident
-        int cap = (num_sms() * 2) / ranks;
+    const void* fn;
+    if (oneshot) fn = a.wire_bf16 ? (const void*)fedavg_oneshot_kernel<true> : (const void*)fedavg_oneshot_kernel<false>;
+    else fn = a.wire_bf16 ? (const void*)fedavg_twoshot_kernel<true> : (const void*)fedavg_twoshot_kernel<false>;
+    if (ranks > 1) {   // emulated ranks share one GPU: the cooperative launch needs the whole grid co-resident
+        int per_sm = 1;
+        CS_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, kCommThreads, 0));
+        int cap = (num_sms() * (per_sm < 1 ? 1 : per_sm)) / ranks;
         if (nb > cap) nb = cap < 1 ? 1 : cap;
     }
     dim3 grid(nb, ranks), block(kCommThreads);
     void* args[] = {(void*)&ctxs, (void*)&a};
-    const void* fn;
-    if (oneshot) fn = a.wire_bf16 ? (const void*)fedavg_oneshot_kernel<true> : (const void*)fedavg_oneshot_kernel<false>;
-    else fn = a.wire_bf16 ? (const void*)fedavg_twoshot_kernel<true> : (const void*)fedavg_twoshot_kernel<false>;
     if (ranks > 1) {   // emulation: every rank's blocks must be co-resident -> cooperative launch
         CS_CUDA_OK(cudaLaunchCooperativeKernel(fn, grid, block, args, 0, st));
     } else {

@@ -78,8 +78,57 @@ def test_bench_two_gpus(tmp_path):
         pytest.skip("needs 2 GPUs")
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
            "--master-port", "29731", os.path.join(REPO, "bench.py"), "--gpus", "2", "--steps", "3", "--warmup", "3",
-           "--num-windows", "8192"]
+           "--num-windows", "16384"]
     r = subprocess.run(cmd, cwd=REPO, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     out = json.loads([l for l in r.stdout.splitlines() if l.startswith("{")][-1])
     assert out["n_gpus"] == 2 and out["value"] > 0 and out["comm_status"] == 0 and out["e2e"]["value"] > 0
+
+
+GRAD_WORKER = r'''
+import os, sys, json
+sys.path.insert(0, os.environ["CS_REPO"])
+import torch, torch.distributed as dist
+from crossscale.parallel import launch
+from crossscale.fl.engine import KernelLocalTrainer
+from crossscale.models.resnet1d_wide import resnet1d_small
+from crossscale.data.synth import make_mitbih_like_beats
+rank, world, lr = launch.init_distributed()
+dev = torch.device("cuda", lr); torch.cuda.set_device(dev)
+torch.manual_seed(0)                                   # identical initial model on every rank
+model = resnet1d_small(5).to(dev)
+tr = KernelLocalTrainer(model, dev, lr=5e-2, sync_grads=True, bucket_bytes=8 << 10)
+x, y = make_mitbih_like_beats(256, 360, 5, seed=100 + rank)   # different data per rank
+x, y = torch.from_numpy(x).to(dev).unsqueeze(1), torch.from_numpy(y).to(dev)
+for step in range(5):
+    tr.step(x[step * 32:(step + 1) * 32], y[step * 32:(step + 1) * 32])
+torch.cuda.synchronize()
+flat = tr.flat.flat
+allp = [torch.empty_like(flat) for _ in range(world)]
+dist.all_gather(allp, flat)
+ident = all(torch.equal(allp[0], p) for p in allp)      # synchronous DP keeps replicas bit-identical
+# reference: same run with NCCL all-reduce of the flat gradient
+torch.manual_seed(0)
+m2 = resnet1d_small(5).to(dev)
+tr2 = KernelLocalTrainer(m2, dev, lr=5e-2, sync_grads=False)
+for step in range(5):
+    m2.train(); tr2.flat.grad.zero_()
+    loss = torch.nn.functional.cross_entropy(m2(x[step * 32:(step + 1) * 32]).float(), y[step * 32:(step + 1) * 32])
+    loss.backward()
+    dist.all_reduce(tr2.flat.grad); tr2.flat.grad.mul_(1.0 / world)
+    tr2.mom.mul_(0.9).add_(tr2.flat.grad); tr2.flat.flat.add_(tr2.mom, alpha=-5e-2)
+err = float((flat - tr2.flat.flat).abs().max() / (tr2.flat.flat.abs().max()))
+if rank == 0:
+    print("RESULT " + json.dumps({"identical": ident, "rel_err_vs_nccl": err, "status": tr.sync.comm.status(),
+                                  "buckets": len(tr.sync.buckets)}))
+launch.shutdown()
+'''
+
+
+def test_grad_sync_two_gpus(tmp_path):
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    r = _run(2, GRAD_WORKER, tmp_path, 29741)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    res = json.loads([l for l in r.stdout.splitlines() if l.startswith("RESULT ")][-1][7:])
+    assert res["identical"] and res["status"] == 0 and res["buckets"] >= 2 and res["rel_err_vs_nccl"] < 2e-2, res
