@@ -1,0 +1,51 @@
+"""Regenerate profiles/sass/: per-kernel mnemonic histograms + excerpts from `cuobjdump -sass`."""
+import collections
+import os
+import re
+import subprocess
+import sys
+
+REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+LIB = os.path.join(REPO, "lib", "libcrossscale_cuda.so")
+OUT = os.path.join(REPO, "profiles", "sass")
+KERNELS = ["tiny_umma_kernelILi4ELb0ELi2E", "tiny_umma_kernelILi4ELb1ELi2E", "tiny_ecg_f32_kernelILi2E", "conv1d_fwd_kernel",
+           "conv1d_wgrad_kernel", "fedavg_oneshot_kernelILb0E", "fedavg_twoshot_kernelILb0E", "fedavg_twoshot_kernelILb1E"]
+MN = re.compile(r"^\s+/\*[0-9a-f]{4,5}\*/\s+(?:@!?U?P\d+\s+)?([A-Za-z0-9_.]+)")
+KEEP = re.compile(r"UTC|LDTM|STTM|UTMA|SYNCS|REDG|ATOMG|MEMBAR|ERRBAR|ELECT|ACQBULK|UBLKCP|FFMA$|HMMA|.*\.SYS")
+
+HEAD = """# SASS evidence (`cuobjdump -sass lib/libcrossscale_cuda.so`, sm_100a)
+
+Histogram of the tensor-core / TMA / TMEM / NVLink-relevant mnemonics per kernel.
+`UTCHMMA` = tcgen05.mma kind::f16, `LDTM` = tcgen05.ld, `UTCBAR` = tcgen05.commit, `UTCATOMSWS` = tcgen05.alloc/dealloc,
+`UTMALDG.4D` = cp.async.bulk.tensor.4d (TMA), `SYNCS.*` = mbarrier, `REDG.E.ADD.F32x4` = red.global.add.v4.f32,
+`STG/LDG.E.STRONG.SYS` + `MEMBAR.*.SYS` = the st.release.sys / ld.acquire.sys flag protocol of the cross-GPU barrier
+(the data loads/stores on peer-mapped pointers are ordinary `LDG`/`STG`: the address aperture routes them over NVLink).
+"""
+
+
+def main():
+    os.makedirs(OUT, exist_ok=True)
+    sass = subprocess.run(["cuobjdump", "-sass", LIB], capture_output=True, text=True).stdout
+    md = [HEAD]
+    for f in re.split(r"\n\s*Function : ", sass)[1:]:
+        name = f.split("\n", 1)[0].strip()
+        if not any(k in name for k in KERNELS):
+            continue
+        lines = f.split("\n")
+        cnt = collections.Counter(m.group(1) for m in map(MN.match, lines) if m)
+        md.append(f"\n## `{name}`\n\ntotal SASS instructions: {sum(cnt.values())}\n\n| mnemonic | count |\n|---|---|")
+        md += [f"| {k} | {cnt[k]} |" for k in sorted((k for k in cnt if KEEP.match(k)), key=lambda k: -cnt[k])]
+        pick = [i for i, l in enumerate(lines) if "UTCHMMA" in l or "UTMALDG" in l or ".SYS" in l]
+        if pick:
+            lo = max(0, pick[0] - 12)
+            ex = [l[:130].rstrip() for l in lines[lo:lo + 70] if re.search(r"/\*[0-9a-f]{4,5}\*/\s+\S", l)]
+            short = re.sub(r"[^A-Za-z0-9]+", "_", name)[:60]
+            with open(os.path.join(OUT, short + ".sass.txt"), "w") as fh:
+                fh.write(f"// excerpt of {name} around its first tensor-core / TMA / system-scope instruction\n" + "\n".join(ex) + "\n")
+    with open(os.path.join(OUT, "README.md"), "w") as fh:
+        fh.write("\n".join(md) + "\n")
+    print("wrote", OUT)
+
+
+if __name__ == "__main__":
+    sys.exit(main())
