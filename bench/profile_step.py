@@ -50,5 +50,5 @@ g = np.array(pt[64:64 + 2 * a.batch]).reshape(-1, 2)
 t0 = g[:, 0].min()
 print("CTA start ns: min 0 max", g[:, 0].max() - t0, "| CTA ticket ns: min", g[:, 1].min() - t0, "median", int(np.median(g[:, 1])) - t0,
       "max", g[:, 1].max() - t0, "| tail end ns", pt[40] - t0, "last CTA", pt[41])
-print("tail ns: start", pt[46]-t0, "loaded", pt[42]-t0, "checked", pt[43]-t0, "updated", pt[44]-t0, "zeroed", pt[45]-t0, "end", pt[40]-t0)
+print("tail ns: start", pt[46]-t0, "replicas summed", pt[47]-t0, "synced", pt[48]-t0, "gathered", pt[42]-t0, "checked", pt[43]-t0, "updated", pt[44]-t0, "zeroed", pt[45]-t0, "end", pt[40]-t0)
 print(f"amp={a.amp} B={a.batch} L={a.L}: {e0.elapsed_time(e1) / a.steps * 1e3:.2f} us/step (eager launches), loss_sum={st.loss_sum():.4f}")

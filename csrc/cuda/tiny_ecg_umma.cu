@@ -57,7 +57,7 @@ __device__ __forceinline__ int wgrad_row_of_thread(int t) {
 constexpr int kScratchReps = 4;
 constexpr int kScratchStride = 1792;
 constexpr int kScrGB = 1280, kScrGH = 1536;
-__host__ __device__ inline int scratch_offset(int i) {     // flat parameter index -> scratch offset
+__host__ __device__ constexpr int scratch_offset(int i) {     // flat parameter index -> scratch offset
     if (i < TinyLayout::B1) return kScrGB + (i % 7) * 32 + i / 7;
     if (i < TinyLayout::W2) return kScrGB + 7 * 32 + (i - TinyLayout::B1);
     if (i < TinyLayout::B2) {
@@ -67,6 +67,17 @@ __host__ __device__ inline int scratch_offset(int i) {     // flat parameter ind
     if (i < TinyLayout::WH) return kScrGB + 7 * 32 + 16 + (i - TinyLayout::B2);
     return kScrGH + (i - TinyLayout::WH);
 }
+// parameter index -> scratch offset as a table (the tail gathers 13 values per thread; the divisions in
+// scratch_offset() cost more than the whole L2 round trip when done on the critical path)
+constexpr int kOfsTableLen = TinyLayout::WH + 17 * kTinyMaxC;
+struct alignas(16) OfsTable { uint16_t v[(kOfsTableLen + 7) & ~7]; };
+constexpr OfsTable make_ofs_table() {
+    OfsTable t{};
+    for (int i = 0; i < kOfsTableLen; ++i) t.v[i] = (uint16_t)scratch_offset(i);
+    return t;
+}
+__device__ const OfsTable g_ofs_table = make_ofs_table();
+
 __device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, float d) {
     asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
@@ -85,56 +96,87 @@ template <int SETS> __device__ __forceinline__ void load_sum_sets(uint32_t taddr
     }
 }
 
-// Last-CTA tail of the tcgen05 training kernel.  Phase 1 sums the replicas in scratch order (fully
-// coalesced: consecutive threads read consecutive floats) into shared memory; phase 2 walks the
-// parameters in order (coalesced params / momentum), gathering its gradient from shared memory.
-// All global loads of a phase are issued before any dependent use: two L2 round trips in total.
-__device__ __forceinline__ void umma_sgd_tail(const TinyArgs& a, int P, float* sg /* smem, kScratchStride floats */) {
-    constexpr int NV = (TinyLayout::WH + 17 * kTinyMaxC + kUThreads - 1) / kUThreads;
-    constexpr int NS = kScratchStride / kUThreads;         // 14 scratch floats per thread
+// Last-CTA tail of the tcgen05 training kernel.  Phase 1 sums the replicas in scratch order with 16-byte
+// loads (fully coalesced) into shared memory (row stride 33 to spread banks); phase 2 walks the
+// parameters four at a time (16-byte params / momentum accesses) and gathers its gradients from shared
+// memory through a precomputed offset table.  Every global load is issued before its first use.
+// params / mom must be allocated to a multiple of 4 floats (the model's flat arena is).
+__device__ __forceinline__ int sg_index(int o) { return o + (o >> 5); }
+
+__device__ __forceinline__ void umma_sgd_tail(const TinyArgs& a, int P, float* sg /* smem, 33/32 * kScratchStride floats */) {
+    constexpr int S4 = kScratchStride / 4;                              // float4 groups per replica (448)
+    constexpr int NS4 = (S4 + kUThreads - 1) / kUThreads;               // 4
+    constexpr int P4MAX = (kOfsTableLen + 3) / 4;
+    constexpr int NV4 = (P4MAX + kUThreads - 1) / kUThreads;            // 4
     const int t = threadIdx.x;
+    const int P4 = (P + 3) >> 2;
     const float4 fs = __ldcg(reinterpret_cast<const float4*>(a.fstate));     // loss_sum, scale, last, loss_step
     const int4 cs4 = __ldcg(reinterpret_cast<const int4*>(a.ctrl));          // ticket, growth, steps, skipped
+    float4 v[kScratchReps][NS4], p[NV4], m[NV4];
+    uint2 of[NV4];
+#pragma unroll
+    for (int r = 0; r < kScratchReps; ++r)
+#pragma unroll
+        for (int j = 0; j < NS4; ++j) {
+            const int q = j * kUThreads + t;
+            v[r][j] = q < S4 ? __ldcg(reinterpret_cast<const float4*>(a.gacc + r * kScratchStride) + q) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+#pragma unroll
+    for (int j = 0; j < NV4; ++j) {
+        const int q = j * kUThreads + t;
+        p[j] = m[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+        of[j] = make_uint2(0, 0);
+        if (q < P4) {
+            p[j] = reinterpret_cast<const float4*>(a.params)[q];
+            m[j] = reinterpret_cast<const float4*>(a.mom)[q];
+            of[j] = reinterpret_cast<const uint2*>(g_ofs_table.v)[q];
+        }
+    }
     const float scale = a.use_scaler ? fs.y : 1.0f;
     const float inv = 1.0f / scale;
-    {
-        float acc[NS];
 #pragma unroll
-        for (int j = 0; j < NS; ++j) acc[j] = 0.0f;
+    for (int j = 0; j < NS4; ++j) {
+        const int q = j * kUThreads + t;
+        if (q < S4) {
+            float4 acc = v[0][j];
 #pragma unroll
-        for (int r = 0; r < kScratchReps; ++r)
-#pragma unroll
-            for (int j = 0; j < NS; ++j) acc[j] += __ldcg(a.gacc + r * kScratchStride + j * kUThreads + t);
-#pragma unroll
-        for (int j = 0; j < NS; ++j) sg[j * kUThreads + t] = acc[j];
+            for (int r = 1; r < kScratchReps; ++r) { acc.x += v[r][j].x; acc.y += v[r][j].y; acc.z += v[r][j].z; acc.w += v[r][j].w; }
+            const int o = sg_index(4 * q);                              // 4 consecutive offsets stay inside one row
+            sg[o] = acc.x; sg[o + 1] = acc.y; sg[o + 2] = acc.z; sg[o + 3] = acc.w;
+        }
     }
-    float g[NV], p[NV], m[NV];
-#pragma unroll
-    for (int j = 0; j < NV; ++j) {
-        const int i = t + j * kUThreads;
-        p[j] = 0.0f; m[j] = 0.0f;
-        if (i < P) { p[j] = a.params[i]; m[j] = a.mom[i]; }
-    }
+    TAILSTAMP(47);
     __syncthreads();
-#pragma unroll
-    for (int j = 0; j < NV; ++j) {
-        const int i = t + j * kUThreads;
-        g[j] = i < P ? sg[scratch_offset(i)] * inv : 0.0f;
-    }
-    TAILSTAMP(42);
+    TAILSTAMP(48);
+    float4 g[NV4];
     int bad = 0;
 #pragma unroll
-    for (int j = 0; j < NV; ++j) if (!finite_f(g[j])) bad = 1;
+    for (int j = 0; j < NV4; ++j) {
+        const int q = j * kUThreads + t, i = 4 * q;
+        g[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (q < P4) {
+            g[j].x = sg[sg_index(of[j].x & 0xffff)] * inv;
+            if (i + 1 < P) g[j].y = sg[sg_index(of[j].x >> 16)] * inv;
+            if (i + 2 < P) g[j].z = sg[sg_index(of[j].y & 0xffff)] * inv;
+            if (i + 3 < P) g[j].w = sg[sg_index(of[j].y >> 16)] * inv;
+        }
+        if (!finite_f(g[j].x) || !finite_f(g[j].y) || !finite_f(g[j].z) || !finite_f(g[j].w)) bad = 1;
+    }
+    TAILSTAMP(42);
     bad = __syncthreads_or(bad);
     TAILSTAMP(43);
     if (!bad) {
 #pragma unroll
-        for (int j = 0; j < NV; ++j) {
-            const int i = t + j * kUThreads;
-            if (i < P) {
-                const float mm = a.momentum * m[j] + (g[j] + a.wd * p[j]);
-                a.mom[i] = mm;
-                a.params[i] = p[j] - a.lr * mm;
+        for (int j = 0; j < NV4; ++j) {
+            const int q = j * kUThreads + t;
+            if (q < P4) {
+                float4 mm, pp;
+                mm.x = a.momentum * m[j].x + (g[j].x + a.wd * p[j].x); pp.x = p[j].x - a.lr * mm.x;
+                mm.y = a.momentum * m[j].y + (g[j].y + a.wd * p[j].y); pp.y = p[j].y - a.lr * mm.y;
+                mm.z = a.momentum * m[j].z + (g[j].z + a.wd * p[j].z); pp.z = p[j].z - a.lr * mm.z;
+                mm.w = a.momentum * m[j].w + (g[j].w + a.wd * p[j].w); pp.w = p[j].w - a.lr * mm.w;
+                reinterpret_cast<float4*>(a.mom)[q] = mm;
+                reinterpret_cast<float4*>(a.params)[q] = pp;
             }
         }
     }
@@ -215,6 +257,7 @@ __device__ __forceinline__ float warp_reduce16(const float (&p)[16], int lane) {
     v += __shfl_xor_sync(0xffffffffu, v, 1);
     return v;
 }
+
 
 template <int TILES, bool FP16, int MODE>
 __global__ void __launch_bounds__(kUThreads) tiny_umma_kernel(TinyArgs a) {
