@@ -31,7 +31,7 @@ namespace cs {
 
 using namespace tc;
 
-constexpr int kUThreads = 128;
+constexpr int kUThreads = 256;   // 8 warps: warps w and w+4 share TMEM lane quadrant w%4 and split the position tiles
 long long* g_tiny_prof = nullptr;
 __device__ __forceinline__ unsigned long long gtimer() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
 #define TSTAMP(k) do { if (a.prof && blockIdx.x == 0 && threadIdx.x == 0) a.prof[k] = clock64(); } while (0)
@@ -42,9 +42,9 @@ __device__ __forceinline__ unsigned long long gtimer() { unsigned long long t; a
 // TMEM lane that holds accumulator row r: M=128 -> lane r; M=64 -> 16 lanes per 32-lane subpartition
 __device__ __forceinline__ int wgrad_row_of_thread(int t) {
 #if CS_TINY_WGRAD_M == 128
-    return t;
+    return t & 127;
 #else
-    return (t & 31) < 16 ? (t >> 5) * 16 + (t & 15) : -1;
+    return (t & 31) < 16 ? ((t >> 5) & 3) * 16 + (t & 15) : -1;
 #endif
 }
 
@@ -93,6 +93,20 @@ template <int SETS> __device__ __forceinline__ void load_sum_sets(uint32_t taddr
         tmem_ld_wait();
 #pragma unroll
         for (int n = 0; n < 32; ++n) out[n] += __uint_as_float(v[n]);
+    }
+}
+
+// 16 columns summed over SETS rotating accumulator sets that sit 32 columns apart
+template <int SETS> __device__ __forceinline__ void load_sum_sets16(uint32_t taddr, float (&out)[16]) {
+#pragma unroll
+    for (int n = 0; n < 16; ++n) out[n] = 0.0f;
+#pragma unroll
+    for (int q = 0; q < SETS; ++q) {
+        uint32_t v[16];
+        tmem_ld16(taddr + q * 32, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int n = 0; n < 16; ++n) out[n] += __uint_as_float(v[n]);
     }
 }
 
@@ -202,7 +216,7 @@ template <int TILES> struct USmem {
     static constexpr int PLANE = ROWS * 16;                // bytes
     static constexpr int OFF_BAR = 0;                      // 3 mbarriers, tmem slot, flags
     static constexpr int OFF_F32 = 64;                     // fp32 scalars (see F32_* below)
-    static constexpr int F32_COUNT = 112 + 16 + 16 + 128 + 8 + 16 + 8 + 16 + 64;
+    static constexpr int F32_COUNT = 112 + 16 + 16 + 128 + 8 + 16 + 8 + 16 + 128;
     static constexpr int OFF_WT = (OFF_F32 + F32_COUNT * 4 + 127) & ~127;   // 10 weight tiles x 512 B
     static constexpr int OFF_XS = OFF_WT + 10 * 512;
     static constexpr int XS_LEN = TILES * 128 + 8;
@@ -260,10 +274,12 @@ __device__ __forceinline__ float warp_reduce16(const float (&p)[16], int lane) {
 
 
 template <int TILES, bool FP16, int MODE>
-__global__ void __launch_bounds__(kUThreads) tiny_umma_kernel(TinyArgs a) {
+__global__ void __launch_bounds__(kUThreads, TILES <= 4 ? 2 : 1) tiny_umma_kernel(TinyArgs a) {
     using S = USmem<TILES>;
+    constexpr int TPT = TILES / 2;                         // position tiles per thread
     extern __shared__ __align__(128) uint8_t smem[];
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const int row = t & 127, half = t >> 7;                // TMEM lane of this thread / which half of the tiles it owns
     const int L = a.L, C = a.C;
     const int tiles = (L + 127) >> 7;
     TSTAMP(0);
@@ -283,18 +299,18 @@ __global__ void __launch_bounds__(kUThreads) tiny_umma_kernel(TinyArgs a) {
     const float* prm = a.params;
 
     // ---- the first window's loads are issued before anything else: they overlap the whole prologue ----
-    float xin[TILES];
+    float xin[TPT];
     int label = 0;
     auto prefetch_sample = [&](int s) {
-        const int64_t row = a.idx ? a.idx[s] : (int64_t)s;
+        const int64_t drow = a.idx ? a.idx[s] : (int64_t)s;          // dataset row of sample s
 #pragma unroll
-        for (int i = 0; i < TILES; ++i) {
-            const int l = i * 128 + t;
-            xin[i] = 0.0f;
-            if (l < L) xin[i] = a.x_bf16 ? __bfloat162float(((const __nv_bfloat16*)a.x)[row * L + l])
-                                         : __ldg((const float*)a.x + row * L + l);
+        for (int ii = 0; ii < TPT; ++ii) {
+            const int l = (half * TPT + ii) * 128 + row;
+            xin[ii] = 0.0f;
+            if (l < L) xin[ii] = a.x_bf16 ? __bfloat162float(((const __nv_bfloat16*)a.x)[drow * L + l])
+                                          : __ldg((const float*)a.x + drow * L + l);
         }
-        if (MODE == MODE_TRAIN && warp == 0) label = (int)a.y[row];
+        if (MODE == MODE_TRAIN && warp == 0) label = (int)a.y[drow];
     };
     if ((int)blockIdx.x < a.B) prefetch_sample(blockIdx.x);
 
@@ -304,7 +320,12 @@ __global__ void __launch_bounds__(kUThreads) tiny_umma_kernel(TinyArgs a) {
         const int n16 = (S::TOTAL - S::OFF_XS) / 16;
         for (int i = t; i < n16; i += kUThreads) z[i] = make_uint4(0, 0, 0, 0);
     }
-    // Programmatic dependent launch: everything above (window prefetch, smem clear) may run while the
+    if (t == 0) {
+        mbar_init(bar_fwd, 1); mbar_init(bar_dg, 1); mbar_init(bar_wg, 1);
+        fence_mbar_init();
+    }
+    if (warp == 0) tmem_alloc(tmem_slot, S::TMEM_COLS);
+    // Programmatic dependent launch: everything above (window prefetch, smem clear, TMEM allocation) may run while the
     // previous step's kernel is still finishing; parameters / scaler state are read only after it has
     // completed and flushed.  (No-op when the launch carries no programmatic dependency.)
     if (MODE == MODE_TRAIN) asm volatile("griddepcontrol.wait;" ::: "memory");
@@ -333,11 +354,6 @@ __global__ void __launch_bounds__(kUThreads) tiny_umma_kernel(TinyArgs a) {
             else if (i < P) bhs[i - TinyLayout::WH - 16 * C] = pv[j];
         }
     }
-    if (t == 0) {
-        mbar_init(bar_fwd, 1); mbar_init(bar_dg, 1); mbar_init(bar_wg, 1);
-        fence_mbar_init();
-    }
-    if (warp == 0) tmem_alloc(tmem_slot, S::TMEM_COLS);
     fence_proxy_async_smem();
     tc_fence_before_sync();
     __syncthreads();
@@ -346,7 +362,7 @@ __global__ void __launch_bounds__(kUThreads) tiny_umma_kernel(TinyArgs a) {
     // let the next step's grid start its own prologue on SMs as they drain
     if (MODE == MODE_TRAIN) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     TSTAMP(1);
-    const uint32_t tmem_lane = tmem_base + ((uint32_t)(warp * 32) << 16);
+    const uint32_t tmem_lane = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
     const uint32_t col_w = 16 * TILES, col_b = 16 * TILES + 64;
 
     const uint32_t s_base = smem_u32(smem);
@@ -359,7 +375,7 @@ __global__ void __launch_bounds__(kUThreads) tiny_umma_kernel(TinyArgs a) {
 
     const float invL = 1.0f / (float)L, invB = 1.0f / (float)a.B;
     const float lscale = (MODE == MODE_TRAIN && a.use_scaler) ? a.fstate[FS_SCALE] : 1.0f;
-    float ghead0 = 0.0f, ghead1 = 0.0f, loss_acc = 0.0f;
+    float ghead0 = 0.0f, loss_acc = 0.0f;
     uint32_t it = 0;
 
     for (int s = blockIdx.x; s < a.B; s += gridDim.x, ++it) {
@@ -368,19 +384,19 @@ __global__ void __launch_bounds__(kUThreads) tiny_umma_kernel(TinyArgs a) {
         const int cur_label = label;
         if (MODE != MODE_FWD && it > 0) mbar_wait(bar_wg, par ^ 1);   // previous sample's MMAs released the planes
 #pragma unroll
-        for (int i = 0; i < TILES; ++i) { const int l = i * 128 + t; if (l < L) xs[l + 3] = round_half<FP16>(xin[i]); }
+        for (int ii = 0; ii < TPT; ++ii) { const int l = (half * TPT + ii) * 128 + row; if (l < L) xs[l + 3] = round_half<FP16>(xin[ii]); }
         if (s + (int)gridDim.x < a.B) prefetch_sample(s + gridDim.x);   // next window loads during this one
         __syncthreads();
         if (it == 0) TSTAMP(2);
 
         // ---- P2: conv1 + ReLU on FFMA -> h1 planes; im2col(x)+ones -> xcol plane ------------------
         {
-            float xv[TILES][7];
+            float xv[TPT][7];
 #pragma unroll
-            for (int i = 0; i < TILES; ++i)
+            for (int i = 0; i < TPT; ++i)
 #pragma unroll
-                for (int k = 0; k < 7; ++k) xv[i][k] = xs[i * 128 + t + k];
-            uint32_t hp[TILES][8];
+                for (int k = 0; k < 7; ++k) xv[i][k] = xs[(half * TPT + i) * 128 + row + k];
+            uint32_t hp[TPT][8];
 #pragma unroll
             for (int c = 0; c < 16; c += 2) {
                 float w0[7], w1[7];
@@ -388,7 +404,7 @@ __global__ void __launch_bounds__(kUThreads) tiny_umma_kernel(TinyArgs a) {
                 for (int k = 0; k < 7; ++k) { w0[k] = w1s[c * 7 + k]; w1[k] = w1s[(c + 1) * 7 + k]; }
                 const float bb0 = b1s[c], bb1 = b1s[c + 1];
 #pragma unroll
-                for (int i = 0; i < TILES; ++i) {
+                for (int i = 0; i < TPT; ++i) {
                     float a0 = bb0, a1 = bb1;
 #pragma unroll
                     for (int k = 0; k < 7; ++k) { a0 = fmaf(w0[k], xv[i][k], a0); a1 = fmaf(w1[k], xv[i][k], a1); }
@@ -396,8 +412,8 @@ __global__ void __launch_bounds__(kUThreads) tiny_umma_kernel(TinyArgs a) {
                 }
             }
 #pragma unroll
-            for (int i = 0; i < TILES; ++i) {
-                const int l = i * 128 + t;
+            for (int i = 0; i < TPT; ++i) {
+                const int l = (half * TPT + i) * 128 + row;
                 if (l < L) {
                     const int ro = (l + 8) * 16;
                     *reinterpret_cast<uint4*>(smem + S::P_H1 + ro) = make_uint4(hp[i][0], hp[i][1], hp[i][2], hp[i][3]);
@@ -436,15 +452,16 @@ __global__ void __launch_bounds__(kUThreads) tiny_umma_kernel(TinyArgs a) {
         float pool[16];
 #pragma unroll
         for (int c = 0; c < 16; ++c) pool[c] = 0.0f;
-        uint32_t mask[TILES];
+        uint32_t mask[TPT];
 #pragma unroll
-        for (int i = 0; i < TILES; ++i) {
+        for (int i = 0; i < TPT; ++i) {
             mask[i] = 0;
-            if (i < tiles) {
+            const int ti = half * TPT + i;                 // warp-uniform
+            if (ti < tiles) {
                 uint32_t v[16];
-                tmem_ld16(tmem_lane + i * 16, v);
+                tmem_ld16(tmem_lane + ti * 16, v);
                 tmem_ld_wait();
-                const bool valid = (i * 128 + t) < L;
+                const bool valid = (ti * 128 + row) < L;
 #pragma unroll
                 for (int c = 0; c < 16; ++c) {
                     const float z = __uint_as_float(v[c]) + b2s[c];
@@ -458,7 +475,7 @@ __global__ void __launch_bounds__(kUThreads) tiny_umma_kernel(TinyArgs a) {
         }
         tc_fence_before_sync();
         __syncthreads();
-        if (t < 16) pooled[t] = (red[t] + red[16 + t] + red[32 + t] + red[48 + t]) * invL;
+        if (t < 16) pooled[t] = (red[t] + red[16 + t] + red[32 + t] + red[48 + t] + red[64 + t] + red[80 + t] + red[96 + t] + red[112 + t]) * invL;
         __syncthreads();
         if (it == 0) TSTAMP(6);
 
@@ -495,10 +512,6 @@ __global__ void __launch_bounds__(kUThreads) tiny_umma_kernel(TinyArgs a) {
         // ---- head grads, dp, dz2 = mask * dp / L -> dz2 planes -----------------------------------------------
         if (t < 16 * C) ghead0 = fmaf(dlog[t >> 4], pooled[t & 15], ghead0);
         else if (t < 17 * C) ghead0 += dlog[t - 16 * C];
-        if (t + 128 < 17 * C) {
-            const int u = t + 128;
-            if (u < 16 * C) ghead1 = fmaf(dlog[u >> 4], pooled[u & 15], ghead1); else ghead1 += dlog[u - 16 * C];
-        }
         if (t < 16) {
             float v = 0.0f;
             for (int c = 0; c < C; ++c) v = fmaf(whs[c * 16 + t], dlog[c], v);
@@ -510,8 +523,8 @@ __global__ void __launch_bounds__(kUThreads) tiny_umma_kernel(TinyArgs a) {
 #pragma unroll
             for (int c = 0; c < 16; ++c) g[c] = gj[c];
 #pragma unroll
-            for (int i = 0; i < TILES; ++i) {
-                const int l = i * 128 + t;
+            for (int i = 0; i < TPT; ++i) {
+                const int l = (half * TPT + i) * 128 + row;
                 if (l < L) {
                     uint32_t q[8];
 #pragma unroll
@@ -559,12 +572,13 @@ __global__ void __launch_bounds__(kUThreads) tiny_umma_kernel(TinyArgs a) {
 
         // ---- epilogue 2: dz1 = dh1 * (h1 > 0) -> dz1 planes ---------------------------------------------------
 #pragma unroll
-        for (int i = 0; i < TILES; ++i) {
-            if (i < tiles) {
+        for (int i = 0; i < TPT; ++i) {
+            const int ti = half * TPT + i;
+            if (ti < tiles) {
                 uint32_t v[16];
-                tmem_ld16(tmem_lane + i * 16, v);
+                tmem_ld16(tmem_lane + ti * 16, v);
                 tmem_ld_wait();
-                const int l = i * 128 + t;
+                const int l = ti * 128 + row;
                 if (l < L) {
                     const int ro = (l + 8) * 16;
                     const uint4 ha = *reinterpret_cast<const uint4*>(smem + S::P_H1 + ro);
@@ -607,58 +621,59 @@ __global__ void __launch_bounds__(kUThreads) tiny_umma_kernel(TinyArgs a) {
         mbar_wait(bar_wg, (it - 1) & 1);
         tc_fence_after_sync();
         TSTAMP(13);
+        // Both halves of the CTA read accumulators: half h owns columns [16h, 16h+16) of every 32-column
+        // accumulator set, sums the rotating sets in registers and issues the reductions for its columns.
         const int r = wgrad_row_of_thread(t);             // accumulator row held by this thread's TMEM lane
-        constexpr int kWarpsW = CS_TINY_WGRAD_M == 128 ? 2 : 3;   // warps whose lanes hold rows < 40
+        constexpr int kWarpsW = CS_TINY_WGRAD_M == 128 ? 2 : 3;   // lane quadrants whose lanes hold rows < 40
+        const int wq = warp & 3, n0 = half * 16;
         if (MODE == MODE_TRAIN) {
             float* g = a.gacc + (blockIdx.x % kScratchReps) * kScratchStride;
-            if (warp < kWarpsW) {
-                float v[32];
-                load_sum_sets<2>(tmem_lane + col_w, v);
+            if (wq < kWarpsW) {
+                float v[16];
+                load_sum_sets16<2>(tmem_lane + col_w + n0, v);
                 if (r >= 0 && r < 40) {
 #pragma unroll
-                    for (int n = 0; n < 32; n += 4) red_add_v4(g + r * 32 + n, v[n], v[n + 1], v[n + 2], v[n + 3]);
+                    for (int n = 0; n < 16; n += 4) red_add_v4(g + r * 32 + n0 + n, v[n], v[n + 1], v[n + 2], v[n + 3]);
                 }
             }
-            if (warp == 0) {
-                float v[32];
-                load_sum_sets<4>(tmem_lane + col_b, v);
+            if (wq == 0) {
+                float v[16];
+                load_sum_sets16<4>(tmem_lane + col_b + n0, v);
                 if (r >= 0 && r < 8) {
 #pragma unroll
-                    for (int n = 0; n < 32; n += 4) red_add_v4(g + kScrGB + r * 32 + n, v[n], v[n + 1], v[n + 2], v[n + 3]);
+                    for (int n = 0; n < 16; n += 4) red_add_v4(g + kScrGB + r * 32 + n0 + n, v[n], v[n + 1], v[n + 2], v[n + 3]);
                 }
             }
             if (t < 17 * C) atomicAdd(g + kScrGH + t, ghead0);
-            if (t + 128 < 17 * C) atomicAdd(g + kScrGH + t + 128, ghead1);
         } else {
             float* g = a.gacc;                            // MODE_BWD: plain parameter-order gradient
-            if (warp < kWarpsW) {
-                float v[32];
-                load_sum_sets<2>(tmem_lane + col_w, v);
+            if (wq < kWarpsW) {
+                float v[16];
+                load_sum_sets16<2>(tmem_lane + col_w + n0, v);
                 const int k = r >> 3, c8 = r & 7;
                 if (r >= 0 && r < 40) {
 #pragma unroll
-                    for (int n = 0; n < 32; ++n) {
-                        const int co = n & 15, ci = (n >> 4) * 8 + c8;
-                        atomicAdd(g + TinyLayout::W2 + (co * 16 + ci) * 5 + k, v[n]);
-                    }
+                    for (int co = 0; co < 16; ++co)      // columns n0.. = plane j = half: ci = 8*half + c8
+                        atomicAdd(g + TinyLayout::W2 + (co * 16 + half * 8 + c8) * 5 + k, v[co]);
                 }
             }
-            if (warp == 0) {
-                float v[32];
-                load_sum_sets<4>(tmem_lane + col_b, v);
-                if (r >= 0 && r < 7) {
+            if (wq == 0) {
+                float v[16];
+                load_sum_sets16<4>(tmem_lane + col_b + n0, v);
+                if (half == 0) {                          // columns 0..15: dz1 channels -> dW1 rows / db1
+                    if (r >= 0 && r < 7) {
 #pragma unroll
-                    for (int c = 0; c < 16; ++c) atomicAdd(g + TinyLayout::W1 + c * 7 + r, v[c]);
-                } else if (r == 7) {
+                        for (int c = 0; c < 16; ++c) atomicAdd(g + TinyLayout::W1 + c * 7 + r, v[c]);
+                    } else if (r == 7) {
 #pragma unroll
-                    for (int c = 0; c < 16; ++c) {
-                        atomicAdd(g + TinyLayout::B1 + c, v[c]);
-                        atomicAdd(g + TinyLayout::B2 + c, v[16 + c]);
+                        for (int c = 0; c < 16; ++c) atomicAdd(g + TinyLayout::B1 + c, v[c]);
                     }
+                } else if (r == 7) {                      // columns 16..31: dz2 channels -> db2
+#pragma unroll
+                    for (int c = 0; c < 16; ++c) atomicAdd(g + TinyLayout::B2 + c, v[c]);
                 }
             }
             if (t < 17 * C) atomicAdd(g + TinyLayout::WH + t, ghead0);
-            if (t + 128 < 17 * C) atomicAdd(g + TinyLayout::WH + t + 128, ghead1);
         }
     }
     TSTAMP(14);
