@@ -3,7 +3,7 @@
 Per rank: K rounds of `local_steps` local steps (tcgen05 conv kernels) + one aggregation of the 97 MB fp32
 model.  Reports device-timed local ms/round, aggregation ms/round and the achieved NVLink bandwidth of the
 fused two-shot kernel against a flattened NCCL all-reduce (+ scale) of the same vector and against the
-roofline 2*(P-1)/P*bytes / 770 GB/s (measured peer copy bandwidth, B200_PROFILING.md).
+roofline (P-1)/P*bytes per direction / 770 GB/s (measured peer copy bandwidth, B200_PROFILING.md).
 
     torchrun --nproc-per-node N bench/resnet_fedavg.py [--rounds 3 --local-steps 2 --batch 64 --wire bf16]
 """
@@ -73,7 +73,8 @@ def main():
     t_nccl = timed(nccl)
     if rank == 0:
         es = 2 if a.wire == "bf16" else 4
-        wire_bytes = 2.0 * (world - 1) / world * n * es if world > 1 else 0.0
+        # bytes that cross NVLink PER DIRECTION per GPU (reduce-scatter in, all-gather out run concurrently)
+        wire_bytes = (world - 1) / world * n * es if world > 1 else 0.0
         roof_ms = wire_bytes / 770e9 * 1e3
         print(json.dumps({
             "model": a.model, "params": n, "world": world, "wire": a.wire, "batch": a.batch, "local_steps": a.local_steps,
@@ -81,7 +82,7 @@ def main():
             "samples_per_s_per_client": sum(w["samples_per_s"] for w in rows) / len(rows),
             "agg_ms_in_round": sum(w["comm_ms"] for w in rows) / len(rows),
             "agg_kernel_ms": t_kernel, "agg_nccl_ms": t_nccl, "speedup_vs_nccl": t_nccl / t_kernel,
-            "nvlink_bytes_per_gpu": wire_bytes, "roofline_ms_at_770GBs": roof_ms,
+            "nvlink_bytes_per_direction_per_gpu": wire_bytes, "inplace_symmetric": bool(r.agg.inplace), "roofline_ms_at_770GBs": roof_ms,
             "fraction_of_nvlink_roofline": (roof_ms / t_kernel) if t_kernel > 0 and world > 1 else None,
             "avg_loss": rows[-1]["avg_loss"], "comm_status": r.agg.comm.status()}))
     r.close()

@@ -351,9 +351,13 @@ class FedAvgRunner:
         broadcast_model(self.flat)                       # round 0: common initial model
         if not self.fused:
             self.trainer.load_flat(self.flat)
-        self.prev = self.flat.clone()
         self.agg = FedAvgAggregator(self.numel, self.device, backend=agg_backend, wire=wire,
                                     server_lr=server_lr, reset_momentum=reset_momentum)
+        if self.agg.inplace:                             # large model: parameters move into peer-mapped memory
+            self.trainer.flat.rebind(self.agg.param_view)
+            self.flat = self.trainer.flat.flat
+            self.agg.set_weights(self.weight)
+        self.prev = self.flat.clone()
         self.rows: List[dict] = []
 
     def _events(self):
@@ -462,4 +466,8 @@ class FedAvgRunner:
         return loss
 
     def close(self):
+        if getattr(self.agg, "inplace", False):          # parameters live in the arena: move them out before it is freed
+            torch.cuda.synchronize()
+            self.trainer.flat.rebind(self.flat.clone())
+            self.flat = self.trainer.flat.flat
         self.agg.close()

@@ -51,7 +51,7 @@ def broadcast_model(flat: torch.Tensor, root: int = 0) -> None:
 class FedAvgAggregator:
     def __init__(self, numel: int, device, backend: str = "auto", wire: str = "fp32",
                  server_lr: float = 1.0, reset_momentum: bool = False, channel: int = 0,
-                 comm: Optional[SymmetricComm] = None):
+                 comm: Optional[SymmetricComm] = None, inplace: str = "auto"):
         self.numel, self.device = int(numel), torch.device(device)
         self.wire_bf16 = int(wire == "bf16")
         self.server_lr, self.reset_momentum, self.channel = float(server_lr), bool(reset_momentum), channel
@@ -60,17 +60,45 @@ class FedAvgAggregator:
         self.backend = backend
         self.comm = comm
         self.launches = 0
+        # large fp32 models: keep the parameters IN the arena and aggregate in place (no staging passes)
+        self.inplace = (backend == "kernel" and not self.wire_bf16 and self.numel > 65536 and self.numel % 4 == 0
+                        and inplace in ("auto", "on"))
+        self.param_view: Optional[torch.Tensor] = None
+        self._weights = None
         if backend == "kernel":
-            need = int(_lib.cuda_lib().cs_fedavg_arena_bytes(self.numel, self.wire_bf16, _world()))
+            need = (self.numel * 4 if self.inplace
+                    else int(_lib.cuda_lib().cs_fedavg_arena_bytes(self.numel, self.wire_bf16, _world())))
             if self.comm is None:
                 self.comm = SymmetricComm(need)
             elif self.comm.arena_bytes < need:
                 raise ValueError(f"arena too small: {self.comm.arena_bytes} < {need}")
+            if self.inplace:
+                self.param_view = self.comm.arena_tensor(self.numel)
+
+    def set_weights(self, weight: float) -> None:
+        """in-place mode needs every client's weight on every rank (one host all-gather, set-up time)"""
+        import ctypes as C
+        ws = [float(weight)]
+        if _world() > 1:
+            ws = [None] * _world()
+            dist.all_gather_object(ws, float(weight))
+        self._weights = (C.c_float * len(ws))(*ws)
 
     def aggregate(self, flat: torch.Tensor, prev: torch.Tensor, weight: float,
                   mom: Optional[torch.Tensor] = None) -> None:
         """In place on ``flat`` and ``prev`` (both end up holding the new global model)."""
         n = self.numel
+        if self.backend == "kernel" and self.inplace:
+            if flat.data_ptr() != self.param_view.data_ptr():
+                raise ValueError("in-place aggregation: the parameters must live in aggregator.param_view (FlatParams.rebind)")
+            if self._weights is None:
+                self.set_weights(weight)
+            use_prev = self.server_lr != 1.0
+            _lib.check(_lib.cuda_lib().cs_fedavg_aggregate_inplace(
+                self.comm.handle, 0, prev.data_ptr() if use_prev else None, n, self._weights, self.server_lr,
+                _lib.ptr(mom) if self.reset_momentum else None, self.channel, _lib.stream_ptr()), "cs_fedavg_aggregate_inplace")
+            self.launches += 1
+            return
         if self.backend == "kernel":
             _lib.check(_lib.cuda_lib().cs_fedavg_aggregate(
                 self.comm.handle, flat.data_ptr(), prev.data_ptr(), n, float(weight), self.wire_bf16,

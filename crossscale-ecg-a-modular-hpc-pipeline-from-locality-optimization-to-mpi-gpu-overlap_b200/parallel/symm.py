@@ -43,6 +43,11 @@ class SymmetricComm:
     def handle(self):
         return self._h
 
+    def arena_tensor(self, numel: int, offset_bytes: int = 0, dtype=torch.float32) -> torch.Tensor:
+        """A torch view of this rank's arena (peer-mapped memory): tensors placed here are readable and
+        writable by every peer's kernels at the same offset."""
+        return _arena_view(int(_lib.cuda_lib().cs_comm_arena(self._h)), self.arena_bytes, numel, offset_bytes, dtype)
+
     def barrier(self, channel: int = 0) -> None:
         _lib.check(_lib.cuda_lib().cs_comm_barrier(self._h, channel, _lib.stream_ptr()), "cs_comm_barrier")
 
@@ -83,6 +88,9 @@ class LocalGroup:
     def handles(self):
         return self._arr
 
+    def arena_tensor(self, rank: int, numel: int, offset_bytes: int = 0, dtype=torch.float32) -> torch.Tensor:
+        return _arena_view(int(_lib.cuda_lib().cs_comm_arena(self._arr[rank])), self.arena_bytes, numel, offset_bytes, dtype)
+
     def barrier(self, channel: int = 0) -> None:
         _lib.check(_lib.cuda_lib().cs_comm_barrier(self._arr[0], channel, _lib.stream_ptr()), "cs_comm_barrier")
 
@@ -99,6 +107,19 @@ class LocalGroup:
             torch.cuda.synchronize()
             _lib.cuda_lib().cs_comm_destroy(self._arr[0])
             self._arr = None
+
+
+class _RawCuda:
+    def __init__(self, ptr: int, nbytes: int):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 3}
+
+
+def _arena_view(base: int, arena_bytes: int, numel: int, offset_bytes: int, dtype) -> torch.Tensor:
+    nbytes = numel * torch.empty((), dtype=dtype).element_size()
+    if offset_bytes % 16 or offset_bytes + nbytes > arena_bytes:
+        raise ValueError("arena view out of range / misaligned")
+    raw = torch.as_tensor(_RawCuda(base + offset_bytes, nbytes), device=torch.device("cuda", torch.cuda.current_device()))
+    return raw.view(dtype)
 
 
 def ptr_array(tensors) -> "C.Array":

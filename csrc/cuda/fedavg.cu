@@ -312,6 +312,84 @@ __global__ void __launch_bounds__(kCommThreads) fedavg_twoshot_kernel(const Comm
     if (threadIdx.x == 0) *ep = e0 + 2;
 }
 
+// ------------------------------------------------------------------------------------------------
+// in-place two-shot on symmetric parameters: the model's fp32 parameters LIVE in the arena (same offset
+// on every rank), so there is no staging at all.  Rank r reads slice r of every peer's parameters over
+// NVLink, forms sum_j w_j theta_j (optionally theta_prev + lr * (avg - theta_prev)) and stores the result
+// into slice r of EVERY replica.  Slice r is read only by rank r and written only by rank r, so two
+// barriers (all local training finished / all pushes landed) are the whole protocol.  Per GPU this moves
+// (P-1)/P * n floats in each NVLink direction and touches HBM once — the bandwidth-optimal schedule.
+// ------------------------------------------------------------------------------------------------
+struct InplaceCall {
+    size_t param_off[kMaxRanks];       // byte offset of the parameter vector inside each (emulated) rank's arena
+    float* prev[kMaxRanks];            // optional previous global model (slice-local use only), may be NULL
+    float* mom[kMaxRanks];             // optional buffer zeroed after aggregation
+    float weights[kMaxRanks];          // aggregation weight of every rank (same array on all ranks)
+    long long n;
+    float server_lr;
+    int channel;
+};
+
+__global__ void __launch_bounds__(kCommThreads) fedavg_inplace_kernel(const CommDev* ctxs, InplaceCall a) {
+    const int er = blockIdx.y;
+    const CommDev& c = ctxs[er];
+    const int P = c.world, b = blockIdx.x, nb = gridDim.x, T = blockDim.x, tid = threadIdx.x;
+    uint32_t* ep = c.epochs + (size_t)a.channel * kMaxBlocks + b;
+    const uint32_t e0 = *ep;
+    const long long n4 = a.n >> 2;                           // n is a multiple of 4 (checked on the host)
+    const long long gps = (n4 + P - 1) / P, gpb = (gps + nb - 1) / nb;
+    float* prev = a.prev[er];
+    float* mom = a.mom[er];
+    xgpu_barrier(c, a.channel, b, e0 + 1);                   // every rank's local training is complete
+    {
+        const int s = c.rank;
+        const long long g0 = s * gps + (long long)b * gpb;
+        long long g1 = g0 + gpb; if (g1 > (s + 1) * gps) g1 = (s + 1) * gps; if (g1 > n4) g1 = n4;
+        constexpr int U2 = 2;
+        for (long long g = g0 + tid; g < g1; g += (long long)U2 * T) {
+            float4 r[U2][kMaxRanks], q[U2];
+#pragma unroll
+            for (int u = 0; u < U2; ++u) {
+                const long long gi = g + (long long)u * T;
+#pragma unroll
+                for (int p = 0; p < kMaxRanks; ++p)
+                    if (p < P && gi < g1) {
+                        const int src = (c.rank + p) % P;
+                        r[u][p] = __ldcg(reinterpret_cast<const float4*>(c.arena[src] + a.param_off[er]) + gi);
+                    }
+                if (prev && gi < g1) q[u] = reinterpret_cast<const float4*>(prev)[gi];
+            }
+#pragma unroll
+            for (int u = 0; u < U2; ++u) {
+                const long long gi = g + (long long)u * T;
+                if (gi < g1) {
+                    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                    for (int p = 0; p < kMaxRanks; ++p)
+                        if (p < P) {
+                            const float w = a.weights[(c.rank + p) % P];
+                            acc.x = fmaf(w, r[u][p].x, acc.x); acc.y = fmaf(w, r[u][p].y, acc.y);
+                            acc.z = fmaf(w, r[u][p].z, acc.z); acc.w = fmaf(w, r[u][p].w, acc.w);
+                        }
+                    if (prev) {
+                        acc = make_float4(q[u].x + a.server_lr * (acc.x - q[u].x), q[u].y + a.server_lr * (acc.y - q[u].y),
+                                          q[u].z + a.server_lr * (acc.z - q[u].z), q[u].w + a.server_lr * (acc.w - q[u].w));
+                        reinterpret_cast<float4*>(prev)[gi] = acc;
+                    }
+                    for (int p = 0; p < P; ++p)
+                        reinterpret_cast<float4*>(c.arena[(c.rank + p) % P] + a.param_off[er])[gi] = acc;
+                }
+            }
+        }
+    }
+    if (mom) {                                               // local momentum reset (all slices)
+        for (long long g = (long long)b * T + tid; g < n4; g += (long long)nb * T)
+            reinterpret_cast<float4*>(mom)[g] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    xgpu_barrier(c, a.channel, b, e0 + 2);                   // every push has landed in my replica
+    if (threadIdx.x == 0) *ep = e0 + 2;
+}
+
 __global__ void barrier_kernel(const CommDev* ctxs, int channel) {
     const CommDev& c = ctxs[blockIdx.y];
     uint32_t* ep = c.epochs + (size_t)channel * kMaxBlocks + blockIdx.x;
@@ -488,6 +566,47 @@ int fedavg_aggregate_local(cs_comm** g, int world, float* const* local, float* c
     }
     a.n = n; a.server_lr = server_lr; a.post_scale = post_scale; a.wire_bf16 = wire_bf16; a.channel = channel; a.arena_off = arena_off;
     return launch_agg(g[0]->group_dev, world, world, g[0]->bytes, a, st);
+}
+
+static int launch_inplace(const CommDev* ctxs, int ranks, const InplaceCall& a, cudaStream_t st) {
+    CS_REQUIRE(a.n > 0 && a.n % 4 == 0, "aggregate_inplace: n must be a positive multiple of 4");
+    CS_REQUIRE(a.channel >= 0 && a.channel < kChannels, "aggregate_inplace: bad channel");
+    int nb = pick_blocks(a.n, false);
+    const void* fn = (const void*)fedavg_inplace_kernel;
+    if (ranks > 1) {
+        int per_sm = 1;
+        CS_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, kCommThreads, 0));
+        int cap = (num_sms() * (per_sm < 1 ? 1 : per_sm)) / ranks;
+        if (nb > cap) nb = cap < 1 ? 1 : cap;
+    }
+    dim3 grid(nb, ranks), block(kCommThreads);
+    void* args[] = {(void*)&ctxs, (void*)&a};
+    if (ranks > 1) CS_CUDA_OK(cudaLaunchCooperativeKernel(fn, grid, block, args, 0, st));
+    else CS_CUDA_OK(cudaLaunchKernel(fn, grid, block, args, 0, st));
+    return CS_OK;
+}
+
+int fedavg_aggregate_inplace(cs_comm* c, size_t param_off, float* prev, long long n, const float* weights,
+                             float server_lr, float* mom, int channel, cudaStream_t st) {
+    CS_REQUIRE(c && !c->emulated, "aggregate_inplace: use the *_local entry point for emulated groups");
+    CS_REQUIRE(param_off % 16 == 0 && param_off + (size_t)n * 4 <= c->bytes, "aggregate_inplace: parameters must lie inside the arena");
+    InplaceCall a; memset(&a, 0, sizeof(a));
+    a.param_off[0] = param_off; a.prev[0] = prev; a.mom[0] = mom;
+    for (int r = 0; r < c->world; ++r) a.weights[r] = weights[r];
+    a.n = n; a.server_lr = server_lr; a.channel = channel;
+    return launch_inplace(c->dev, 1, a, st);
+}
+
+int fedavg_aggregate_inplace_local(cs_comm** g, int world, size_t param_off, float* const* prev, long long n,
+                                   const float* weights, float server_lr, float* const* mom, int channel, cudaStream_t st) {
+    CS_REQUIRE(g && g[0] && g[0]->emulated && g[0]->world == world, "aggregate_inplace_local: not an emulated group");
+    CS_REQUIRE(param_off % 16 == 0 && param_off + (size_t)n * 4 <= g[0]->bytes, "aggregate_inplace: parameters must lie inside the arena");
+    InplaceCall a; memset(&a, 0, sizeof(a));
+    for (int r = 0; r < world; ++r) {
+        a.param_off[r] = param_off; a.prev[r] = prev ? prev[r] : nullptr; a.mom[r] = mom ? mom[r] : nullptr; a.weights[r] = weights[r];
+    }
+    a.n = n; a.server_lr = server_lr; a.channel = channel;
+    return launch_inplace(g[0]->group_dev, world, a, st);
 }
 
 int comm_barrier(cs_comm* c, int channel, cudaStream_t st) {

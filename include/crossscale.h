@@ -231,6 +231,19 @@ int cs_fedavg_aggregate_local(cs_comm_t** group, int world, float* const* local,
                               float server_lr, float* const* mom, size_t arena_off, int channel,
                               cs_stream_t stream);
 
+/* K7, zero-staging variant for large models whose fp32 parameters LIVE in the arena at `param_off` (same
+ * offset on every rank): rank r reads slice r of every peer's parameters over NVLink, forms
+ * sum_j weights[j]*theta_j (then prev + server_lr*(avg - prev) when prev != NULL) and stores it into slice r
+ * of every replica — (P-1)/P*n floats per NVLink direction, one HBM pass, two cross-GPU barriers, ONE
+ * launch per rank.  `weights` is a host array of `world` floats (identical on all ranks); n % 4 == 0. */
+int cs_fedavg_aggregate_inplace(cs_comm_t* c, size_t param_off, float* prev, int64_t n,
+                                const float* weights, float server_lr, float* mom, int channel,
+                                cs_stream_t stream);
+int cs_fedavg_aggregate_inplace_local(cs_comm_t** group, int world, size_t param_off,
+                                      float* const* prev, int64_t n, const float* weights,
+                                      float server_lr, float* const* mom, int channel,
+                                      cs_stream_t stream);
+
 /* K8: gradient all-reduce of one bucket, in place: grad <- scale * sum_ranks grad  (fp32 [n]).
  * `arena_off` / `channel` let several buckets be in flight on different streams. */
 int cs_allreduce_bucket(cs_comm_t* c, float* grad, int64_t n, float scale, int wire_bf16,

@@ -61,3 +61,39 @@ def test_allreduce_bucket_mean(world):
     torch.cuda.synchronize()
     assert grp.status() == 0
     grp.close()
+
+
+@pytest.mark.parametrize("world", [2, 8])
+@pytest.mark.parametrize("server_lr", [1.0, 0.5])
+def test_fedavg_inplace_symmetric_parameters(world, server_lr):
+    """Zero-staging variant: parameters live in the peer-mapped arena; rank r reduces slice r and pushes it
+    into every replica."""
+    import ctypes as C
+    from crossscale.ops import _lib
+    from crossscale.parallel.symm import LocalGroup, ptr_array
+    dev, n = torch.device("cuda", 0), (1 << 20) + 64
+    grp = LocalGroup(world, n * 4)
+    thetas = [grp.arena_tensor(r, n) for r in range(world)]
+    torch.manual_seed(world)
+    prev0 = torch.randn(n, device=dev)
+    counts = torch.arange(1, world + 1, dtype=torch.float64)
+    weights = (counts / counts.sum()).tolist()
+    wa = (C.c_float * world)(*weights)
+    for rnd in range(2):
+        for t in thetas:
+            t.copy_(prev0 + 0.01 * torch.randn(n, device=dev))
+        prevs = [prev0.clone() for _ in range(world)]
+        moms = [torch.ones(n, device=dev) for _ in range(world)]
+        avg = sum(w * t.double() for w, t in zip(weights, thetas))
+        want = (prev0.double() + server_lr * (avg - prev0.double())).float()
+        _lib.check(_lib.cuda_lib().cs_fedavg_aggregate_inplace_local(
+            grp.handles, world, 0, ptr_array(prevs) if server_lr != 1.0 else None, n, wa, server_lr, ptr_array(moms), 3,
+            _lib.stream_ptr()))
+        torch.cuda.synchronize()
+        assert grp.status() == 0
+        for r in range(world):
+            torch.testing.assert_close(thetas[r], want, rtol=0, atol=2e-6)
+            assert torch.equal(thetas[r], thetas[0]) and float(moms[r].abs().max()) == 0.0
+        prev0 = thetas[0].clone()
+    del thetas
+    grp.close()
