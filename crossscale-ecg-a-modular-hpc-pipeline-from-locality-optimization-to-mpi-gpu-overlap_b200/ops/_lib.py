@@ -132,6 +132,11 @@ def rt_lib() -> C.CDLL:
                 lib.cs_prefetcher_recycle.argtypes = [vp, i32]
                 lib.cs_prefetcher_destroy.restype = None
                 lib.cs_prefetcher_destroy.argtypes = [vp]
+                lib.cs_rendezvous_allgather.restype = i32
+                lib.cs_rendezvous_allgather.argtypes = [C.c_char_p, C.c_char_p, i32, i32, vp, sz, vp, C.c_double]
+                lib.cs_rendezvous_cleanup.restype = i32
+                lib.cs_rendezvous_cleanup.argtypes = [C.c_char_p, C.c_char_p, i32]
+                lib.cs_rendezvous_last_error.restype = C.c_char_p
                 _rt = lib
     return _rt
 

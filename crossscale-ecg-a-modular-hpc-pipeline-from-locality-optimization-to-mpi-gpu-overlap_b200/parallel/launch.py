@@ -46,6 +46,30 @@ def gather_rows(rows: List[dict]) -> List[dict]:
     return [r for part in out for r in part] if out is not None else []
 
 
+def mpi_avg(value: float) -> float:
+    """Mean of a python scalar over ranks (``mpi_avg``, ``Module_3/part3_mpi_gpu_train.py:78-79``)."""
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
+        return float(value)
+    dev = "cuda" if dist.get_backend() == "nccl" else "cpu"
+    t = torch.tensor([float(value)], dtype=torch.float64, device=dev)
+    dist.all_reduce(t)
+    return float(t.item()) / dist.get_world_size()
+
+
+def file_allgather(directory: str, tag: str, rank: int, world: int, blob: bytes, timeout_s: float = 60.0) -> List[bytes]:
+    """All-gather of a small blob through a shared directory (native ``cs_rendezvous_allgather``): the
+    bootstrap for processes that were not started by torchrun."""
+    import ctypes as C
+    from ..ops import _lib
+    lib = _lib.rt_lib()
+    out = (C.c_char * (len(blob) * world))()
+    rc = lib.cs_rendezvous_allgather(directory.encode(), tag.encode(), rank, world, blob, len(blob), out, float(timeout_s))
+    if rc != 0:
+        raise RuntimeError(lib.cs_rendezvous_last_error().decode())
+    raw = bytes(out.raw)
+    return [raw[i * len(blob):(i + 1) * len(blob)] for i in range(world)]
+
+
 def shutdown() -> None:
     if dist.is_available() and dist.is_initialized():
         dist.destroy_process_group()

@@ -292,6 +292,14 @@ int cs_prefetcher_recycle(cs_prefetcher_t* p, int slot);
 void cs_prefetcher_destroy(cs_prefetcher_t* p);
 const char* cs_rt_last_error(void);
 
+/* File-system rendezvous (libcrossscale_rt.so): all-gather of a small blob per rank through a shared
+ * directory — the one-time exchange of CUDA IPC handles for C callers that do not run under
+ * torch.distributed.  ref: MPI.COMM_WORLD bootstrap, part3_fedavg_overlap_mpi_gpu.py:149-151 */
+int cs_rendezvous_allgather(const char* dir, const char* tag, int rank, int world, const void* blob,
+                            size_t blob_bytes, void* out, double timeout_s);
+int cs_rendezvous_cleanup(const char* dir, const char* tag, int rank);
+const char* cs_rendezvous_last_error(void);
+
 #ifdef __cplusplus
 }
 #endif

@@ -92,3 +92,38 @@ def test_reader_open_shard(synth_shards):
         assert (base, n, l) == (16, 700, 500)
         first = np.frombuffer(mm, dtype=np.float32, count=l, offset=base)
         np.testing.assert_array_equal(first, load_shard(paths[0])[0])
+
+
+def test_file_rendezvous_allgather(tmp_path):
+    """native bootstrap: 4 'ranks' (threads) exchange 64-byte blobs through a directory"""
+    import threading
+    from crossscale.parallel.launch import file_allgather
+    world, out = 4, {}
+
+    def worker(r):
+        out[r] = file_allgather(str(tmp_path / "rdv"), "ipc", r, world, bytes([r]) * 64, timeout_s=20)
+
+    ts = [threading.Thread(target=worker, args=(r,)) for r in range(world)]
+    [t.start() for t in ts]
+    [t.join() for t in ts]
+    for r in range(world):
+        assert out[r] == [bytes([q]) * 64 for q in range(world)]
+    with pytest.raises(RuntimeError):
+        file_allgather(str(tmp_path / "rdv2"), "x", 0, 2, b"a" * 8, timeout_s=0.2)      # peer never shows up
+
+
+def test_mpi4py_shim_single_process():
+    import importlib, sys
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "baseline", "mpi_shim"))
+    try:
+        MPI = importlib.import_module("mpi4py").MPI
+        comm = MPI.COMM_WORLD
+        assert comm.Get_rank() == 0 and comm.Get_size() == 1
+        a = np.arange(5, dtype=np.float32); b = np.empty_like(a)
+        comm.Bcast(a, root=0); comm.Allreduce(a, b, op=MPI.SUM); comm.Barrier()
+        np.testing.assert_array_equal(a, b)
+        assert comm.gather({"x": 1}, root=0) == [{"x": 1}] and comm.allreduce(2.5, op=MPI.SUM) == 2.5
+    finally:
+        sys.path.pop(0)
+        for k in [k for k in sys.modules if k.startswith("mpi4py")]:
+            del sys.modules[k]
