@@ -32,6 +32,7 @@ def main():
     ap.add_argument("--model", default="resnet1d_wide")
     ap.add_argument("--wire", default="fp32")
     ap.add_argument("--sync-grads", action="store_true")
+    ap.add_argument("--inplace", default="auto", choices=["auto", "on", "off", "nvls"])
     ap.add_argument("--agg-iters", type=int, default=10)
     a = ap.parse_args()
     rank, world, lr = launch.init_distributed()
@@ -41,7 +42,7 @@ def main():
     xg, yg = torch.from_numpy(x).to(dev), torch.from_numpy(y).to(dev)
     model = build_model(a.model, 5).to(dev)
     r = FedAvgRunner(model, dev, xg, yg, a.batch, a.local_steps, "G1", rank=rank, world=world, wire=a.wire,
-                     model_name=a.model, sync_grads=a.sync_grads)
+                     model_name=a.model, sync_grads=a.sync_grads, inplace=a.inplace)
     r.run_round(0, record=False)                                           # warm-up
     rows = [r.run_round(i + 1) for i in range(a.rounds)]
     n = r.numel
@@ -82,7 +83,7 @@ def main():
             "samples_per_s_per_client": sum(w["samples_per_s"] for w in rows) / len(rows),
             "agg_ms_in_round": sum(w["comm_ms"] for w in rows) / len(rows),
             "agg_kernel_ms": t_kernel, "agg_nccl_ms": t_nccl, "speedup_vs_nccl": t_nccl / t_kernel,
-            "nvlink_bytes_per_direction_per_gpu": wire_bytes, "inplace_symmetric": bool(r.agg.inplace), "roofline_ms_at_770GBs": roof_ms,
+            "nvlink_bytes_per_direction_per_gpu": wire_bytes, "inplace_symmetric": bool(r.agg.inplace), "nvls": r.agg.nvls is not None, "roofline_ms_at_770GBs": roof_ms,
             "fraction_of_nvlink_roofline": (roof_ms / t_kernel) if t_kernel > 0 and world > 1 else None,
             "avg_loss": rows[-1]["avg_loss"], "comm_status": r.agg.comm.status()}))
     r.close()

@@ -317,7 +317,7 @@ class FedAvgRunner:
                  agg_backend: str = "auto", wire: str = "fp32", server_lr: float = 1.0,
                  reset_momentum: bool = False, use_graph: bool = True,
                  generator: Optional[torch.Generator] = None, model_name: str = "tiny_ecg",
-                 sync_grads: bool = False):
+                 sync_grads: bool = False, inplace: str = "auto"):
         self.device = torch.device(device)
         self.model, self.rank, self.world = model, rank, world
         self.batch, self.local_steps, self.config = batch_size, local_steps, config
@@ -352,7 +352,7 @@ class FedAvgRunner:
         if not self.fused:
             self.trainer.load_flat(self.flat)
         self.agg = FedAvgAggregator(self.numel, self.device, backend=agg_backend, wire=wire,
-                                    server_lr=server_lr, reset_momentum=reset_momentum)
+                                    server_lr=server_lr, reset_momentum=reset_momentum, inplace=inplace)
         if self.agg.inplace:                             # large model: parameters move into peer-mapped memory
             self.trainer.flat.rebind(self.agg.param_view)
             self.flat = self.trainer.flat.flat

@@ -64,6 +64,7 @@ _CUDA_SIGS = {
     "cs_fedavg_aggregate_inplace": (i32, [vp, sz, vp, i64, C.POINTER(f32), f32, vp, i32, vp]),
     "cs_fedavg_aggregate_inplace_local": (i32, [C.POINTER(vp), i32, sz, C.POINTER(vp), i64, C.POINTER(f32), f32,
                                                 C.POINTER(vp), i32, vp]),
+    "cs_fedavg_aggregate_nvls": (i32, [vp, vp, vp, vp, i64, f32, f32, f32, vp, i32, vp]),
     "cs_allreduce_bucket": (i32, [vp, vp, i64, f32, i32, sz, i32, vp]),
     "cs_allreduce_bucket_local": (i32, [C.POINTER(vp), i32, C.POINTER(vp), i64, f32, i32, sz, i32, vp]),
     "cs_stage_h2d": (i32, [vp, vp, sz, vp]),

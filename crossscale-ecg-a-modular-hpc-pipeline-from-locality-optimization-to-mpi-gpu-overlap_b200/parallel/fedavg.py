@@ -61,18 +61,31 @@ class FedAvgAggregator:
         self.comm = comm
         self.launches = 0
         # large fp32 models: keep the parameters IN the arena and aggregate in place (no staging passes)
-        self.inplace = (backend == "kernel" and not self.wire_bf16 and self.numel > 65536 and self.numel % 4 == 0
-                        and inplace in ("auto", "on"))
+        self.inplace = (backend == "kernel" and not self.wire_bf16 and self.numel % 4 == 0
+                        and ((self.numel > 65536 and inplace == "auto") or inplace in ("on", "nvls")))
+        self.nvls = None
         self.param_view: Optional[torch.Tensor] = None
         self._weights = None
+        if self.inplace and inplace == "nvls":
+            # parameters live in a torch symmetric-memory buffer that is also mapped at an NVSwitch multicast
+            # address; torch is used for that allocation / rendezvous only, the collective is our kernel
+            import torch.distributed._symmetric_memory as symm_mem
+            if _world() < 2:
+                raise ValueError("NVLS aggregation needs at least 2 ranks")
+            t = symm_mem.empty(self.numel, dtype=torch.float32, device=self.device)
+            h = symm_mem.rendezvous(t, dist.group.WORLD)
+            if not int(h.multicast_ptr):
+                raise RuntimeError("this system offers no NVLS multicast mapping")
+            self.nvls = (t, h)
+            self.param_view = t
         if backend == "kernel":
-            need = (self.numel * 4 if self.inplace
+            need = (4096 if self.nvls is not None else self.numel * 4 if self.inplace
                     else int(_lib.cuda_lib().cs_fedavg_arena_bytes(self.numel, self.wire_bf16, _world())))
             if self.comm is None:
                 self.comm = SymmetricComm(need)
             elif self.comm.arena_bytes < need:
                 raise ValueError(f"arena too small: {self.comm.arena_bytes} < {need}")
-            if self.inplace:
+            if self.inplace and self.nvls is None:
                 self.param_view = self.comm.arena_tensor(self.numel)
 
     def set_weights(self, weight: float) -> None:
@@ -83,6 +96,8 @@ class FedAvgAggregator:
             ws = [None] * _world()
             dist.all_gather_object(ws, float(weight))
         self._weights = (C.c_float * len(ws))(*ws)
+        # NVLS: the switch computes a plain sum; unequal weights are applied by pre-scaling the local replica
+        self._prescale = 1.0 if max(ws) - min(ws) < 1e-12 * max(ws) else float(weight) * len(ws)
 
     def aggregate(self, flat: torch.Tensor, prev: torch.Tensor, weight: float,
                   mom: Optional[torch.Tensor] = None) -> None:
@@ -94,6 +109,13 @@ class FedAvgAggregator:
             if self._weights is None:
                 self.set_weights(weight)
             use_prev = self.server_lr != 1.0
+            if self.nvls is not None:
+                _lib.check(_lib.cuda_lib().cs_fedavg_aggregate_nvls(
+                    self.comm.handle, flat.data_ptr(), int(self.nvls[1].multicast_ptr), prev.data_ptr() if use_prev else None,
+                    n, self._prescale, 1.0 / _world(), self.server_lr, _lib.ptr(mom) if self.reset_momentum else None,
+                    self.channel, _lib.stream_ptr()), "cs_fedavg_aggregate_nvls")
+                self.launches += 1
+                return
             _lib.check(_lib.cuda_lib().cs_fedavg_aggregate_inplace(
                 self.comm.handle, 0, prev.data_ptr() if use_prev else None, n, self._weights, self.server_lr,
                 _lib.ptr(mom) if self.reset_momentum else None, self.channel, _lib.stream_ptr()), "cs_fedavg_aggregate_inplace")

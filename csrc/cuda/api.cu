@@ -61,6 +61,7 @@ int fedavg_aggregate_local(cs_comm**, int, float* const*, float* const*, long lo
                            float* const*, size_t, int, float, cudaStream_t);
 int fedavg_aggregate_inplace(cs_comm*, size_t, float*, long long, const float*, float, float*, int, cudaStream_t);
 int fedavg_aggregate_inplace_local(cs_comm**, int, size_t, float* const*, long long, const float*, float, float* const*, int, cudaStream_t);
+int fedavg_aggregate_nvls(cs_comm*, float*, void*, float*, long long, float, float, float, float*, int, cudaStream_t);
 void* comm_arena(cs_comm*, int);
 size_t comm_bytes(cs_comm*);
 
@@ -228,6 +229,10 @@ int cs_fedavg_aggregate_inplace(cs_comm_t* c, size_t param_off, float* prev, int
 int cs_fedavg_aggregate_inplace_local(cs_comm_t** group, int world, size_t param_off, float* const* prev, int64_t n,
                                       const float* weights, float server_lr, float* const* mom, int channel, cs_stream_t s) {
     return fedavg_aggregate_inplace_local((cs_comm**)group, world, param_off, prev, n, weights, server_lr, mom, channel, ST(s));
+}
+int cs_fedavg_aggregate_nvls(cs_comm_t* c, float* local, void* multicast, float* prev, int64_t n, float prescale,
+                             float post_scale, float server_lr, float* mom, int channel, cs_stream_t s) {
+    return fedavg_aggregate_nvls((cs_comm*)c, local, multicast, prev, n, prescale, post_scale, server_lr, mom, channel, ST(s));
 }
 int cs_allreduce_bucket(cs_comm_t* c, float* grad, int64_t n, float scale, int wire_bf16, size_t arena_off,
                         int channel, cs_stream_t s) {

@@ -390,6 +390,86 @@ __global__ void __launch_bounds__(kCommThreads) fedavg_inplace_kernel(const Comm
     if (threadIdx.x == 0) *ep = e0 + 2;
 }
 
+// ------------------------------------------------------------------------------------------------
+// NVLS variant of the in-place aggregation: the parameters live in a symmetric buffer that is also mapped
+// through an NVSwitch MULTICAST address.  Rank r pulls the switch-reduced slice r with
+// multimem.ld_reduce (the switch fetches and adds all replicas: N/P floats come in instead of (P-1)N/P),
+// applies the server update and broadcasts it to every replica with ONE multimem.st.  Per GPU and
+// direction that is ~N floats on the wire instead of ~2N(P-1)/P for the peer-to-peer version.
+// Unequal client weights are applied by pre-scaling the local replica (one extra local pass).
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ float4 multimem_ld_reduce_add_f32x4(const void* mc) {
+    float4 v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(mc) : "memory");
+    return v;
+}
+__device__ __forceinline__ void multimem_st_f32x4(void* mc, float4 v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+
+struct NvlsCall {
+    float* local;          // this rank's replica (unicast address inside the symmetric buffer)
+    char* mc;              // multicast address of the same buffer
+    float* prev; float* mom;
+    long long n;
+    float prescale, post_scale, server_lr;
+    int channel;
+};
+
+__global__ void __launch_bounds__(kCommThreads) fedavg_nvls_kernel(const CommDev* ctxs, NvlsCall a) {
+    const CommDev& c = ctxs[0];
+    const int P = c.world, b = blockIdx.x, nb = gridDim.x, T = blockDim.x, tid = threadIdx.x;
+    uint32_t* ep = c.epochs + (size_t)a.channel * kMaxBlocks + b;
+    const uint32_t e0 = *ep;
+    const long long n4 = a.n >> 2;
+    const long long gps = (n4 + P - 1) / P, gpb = (gps + nb - 1) / nb;
+    if (a.prescale != 1.0f) {                                   // theta_i *= w_i * P (so that the plain switch sum / P is the weighted mean)
+        for (int s = 0; s < P; ++s) {
+            const long long g0 = s * gps + (long long)b * gpb;
+            long long g1 = g0 + gpb; if (g1 > (s + 1) * gps) g1 = (s + 1) * gps; if (g1 > n4) g1 = n4;
+            for (long long g = g0 + tid; g < g1; g += T) {
+                float4 v = reinterpret_cast<float4*>(a.local)[g];
+                v.x *= a.prescale; v.y *= a.prescale; v.z *= a.prescale; v.w *= a.prescale;
+                reinterpret_cast<float4*>(a.local)[g] = v;
+            }
+        }
+    }
+    xgpu_barrier(c, a.channel, b, e0 + 1);
+    {
+        const int s = c.rank;
+        const long long g0 = s * gps + (long long)b * gpb;
+        long long g1 = g0 + gpb; if (g1 > (s + 1) * gps) g1 = (s + 1) * gps; if (g1 > n4) g1 = n4;
+        for (long long g = g0 + tid; g < g1; g += (long long)kU * T) {
+            float4 v[kU], q[kU];
+#pragma unroll
+            for (int u = 0; u < kU; ++u) {
+                const long long gi = g + (long long)u * T;
+                if (gi < g1) { v[u] = multimem_ld_reduce_add_f32x4(a.mc + gi * 16); if (a.prev) q[u] = reinterpret_cast<const float4*>(a.prev)[gi]; }
+            }
+#pragma unroll
+            for (int u = 0; u < kU; ++u) {
+                const long long gi = g + (long long)u * T;
+                if (gi < g1) {
+                    float4 o = make_float4(v[u].x * a.post_scale, v[u].y * a.post_scale, v[u].z * a.post_scale, v[u].w * a.post_scale);
+                    if (a.prev) {
+                        o = make_float4(q[u].x + a.server_lr * (o.x - q[u].x), q[u].y + a.server_lr * (o.y - q[u].y),
+                                        q[u].z + a.server_lr * (o.z - q[u].z), q[u].w + a.server_lr * (o.w - q[u].w));
+                        reinterpret_cast<float4*>(a.prev)[gi] = o;
+                    }
+                    multimem_st_f32x4(a.mc + gi * 16, o);
+                }
+            }
+        }
+    }
+    if (a.mom) {
+        for (long long g = (long long)b * T + tid; g < n4; g += (long long)nb * T)
+            reinterpret_cast<float4*>(a.mom)[g] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    xgpu_barrier(c, a.channel, b, e0 + 2);
+    if (threadIdx.x == 0) *ep = e0 + 2;
+}
+
 __global__ void barrier_kernel(const CommDev* ctxs, int channel) {
     const CommDev& c = ctxs[blockIdx.y];
     uint32_t* ep = c.epochs + (size_t)channel * kMaxBlocks + blockIdx.x;
@@ -607,6 +687,21 @@ int fedavg_aggregate_inplace_local(cs_comm** g, int world, size_t param_off, flo
     }
     a.n = n; a.server_lr = server_lr; a.channel = channel;
     return launch_inplace(g[0]->group_dev, world, a, st);
+}
+
+int fedavg_aggregate_nvls(cs_comm* c, float* local, void* mc, float* prev, long long n, float prescale, float post_scale,
+                          float server_lr, float* mom, int channel, cudaStream_t st) {
+    CS_REQUIRE(c && !c->emulated && c->world > 1, "aggregate_nvls: needs a real multi-GPU communicator");
+    CS_REQUIRE(local && mc && n > 0 && n % 4 == 0, "aggregate_nvls: bad buffer / n must be a multiple of 4");
+    CS_REQUIRE((((uintptr_t)local | (uintptr_t)mc) & 15) == 0, "aggregate_nvls: buffers must be 16-byte aligned");
+    CS_REQUIRE(channel >= 0 && channel < kChannels, "aggregate_nvls: bad channel");
+    NvlsCall a;
+    a.local = local; a.mc = (char*)mc; a.prev = prev; a.mom = mom; a.n = n; a.prescale = prescale; a.post_scale = post_scale;
+    a.server_lr = server_lr; a.channel = channel;
+    const CommDev* ctxs = c->dev;
+    fedavg_nvls_kernel<<<pick_blocks(n, false), kCommThreads, 0, st>>>(ctxs, a);
+    CS_CUDA_OK(cudaGetLastError());
+    return CS_OK;
 }
 
 int comm_barrier(cs_comm* c, int channel, cudaStream_t st) {

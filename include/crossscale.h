@@ -244,6 +244,16 @@ int cs_fedavg_aggregate_inplace_local(cs_comm_t** group, int world, size_t param
                                       float server_lr, float* const* mom, int channel,
                                       cs_stream_t stream);
 
+/* K7 over NVLS: `local` is this rank's replica inside a symmetric buffer that is also mapped at the NVSwitch
+ * multicast address `multicast` (e.g. torch.distributed._symmetric_memory: buffer_ptrs[rank] / multicast_ptr).
+ * Rank r pulls the switch-reduced slice r (multimem.ld_reduce), applies post_scale and the optional server
+ * update, and broadcasts it to every replica with multimem.st.  prescale != 1 multiplies the local replica
+ * first (unequal client weights: prescale = w_i * world, post_scale = 1/world).  The communicator only
+ * supplies the cross-GPU barrier flags.  ONE launch per rank; n % 4 == 0. */
+int cs_fedavg_aggregate_nvls(cs_comm_t* c, float* local, void* multicast, float* prev, int64_t n,
+                             float prescale, float post_scale, float server_lr, float* mom,
+                             int channel, cs_stream_t stream);
+
 /* K8: gradient all-reduce of one bucket, in place: grad <- scale * sum_ranks grad  (fp32 [n]).
  * `arena_off` / `channel` let several buckets be in flight on different streams. */
 int cs_allreduce_bucket(cs_comm_t* c, float* grad, int64_t n, float scale, int wire_bf16,

@@ -132,3 +132,57 @@ def test_grad_sync_two_gpus(tmp_path):
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     res = json.loads([l for l in r.stdout.splitlines() if l.startswith("RESULT ")][-1][7:])
     assert res["identical"] and res["status"] == 0 and res["buckets"] >= 2 and res["rel_err_vs_nccl"] < 2e-2, res
+
+
+NVLS_WORKER = r'''
+import os, sys, json
+sys.path.insert(0, os.environ["CS_REPO"])
+import torch, torch.distributed as dist
+from crossscale.parallel import launch
+from crossscale.parallel.fedavg import FedAvgAggregator
+rank, world, lr = launch.init_distributed()
+dev = torch.device("cuda", lr); torch.cuda.set_device(dev)
+n = (1 << 20) + 128
+try:
+    agg = FedAvgAggregator(n, dev, backend="kernel", server_lr=0.5, inplace="nvls")
+except Exception as e:
+    if rank == 0:
+        print("RESULT " + json.dumps({"skipped": str(e)[:200]}))
+    launch.shutdown(); sys.exit(0)
+res = {}
+for equal in (True, False):
+    torch.manual_seed(5)
+    prev = torch.randn(n, device=dev)
+    torch.manual_seed(50 + rank)
+    agg.param_view.copy_(prev + 0.01 * torch.randn(n, device=dev))
+    counts = [1000.0] * world if equal else [1000.0 * (r + 1) for r in range(world)]
+    w = counts[rank] / sum(counts)
+    agg._weights = None
+    d = (agg.param_view.double() - prev.double()) * w
+    dist.all_reduce(d)
+    want = (prev.double() + 0.5 * d).float()
+    p2 = prev.clone()
+    agg.aggregate(agg.param_view, p2, w, None)
+    torch.cuda.synchronize()
+    dist.barrier()
+    err = float((agg.param_view - want).abs().max())
+    same = [torch.empty_like(agg.param_view) for _ in range(world)]
+    dist.all_gather(same, agg.param_view.clone())
+    res["equal" if equal else "weighted"] = {"err": err, "identical": all(torch.equal(same[0], s) for s in same),
+                                             "status": agg.comm.status()}
+if rank == 0:
+    print("RESULT " + json.dumps(res))
+launch.shutdown()
+'''
+
+
+def test_fedavg_nvls_multimem_two_gpus(tmp_path):
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    r = _run(2, NVLS_WORKER, tmp_path, 29751)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    res = json.loads([l for l in r.stdout.splitlines() if l.startswith("RESULT ")][-1][7:])
+    if "skipped" in res:
+        pytest.skip("no NVLS multicast here: " + res["skipped"])
+    for key, v in res.items():
+        assert v["err"] < 2e-6 and v["identical"] and v["status"] == 0, (key, v)
