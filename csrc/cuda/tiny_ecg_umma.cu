@@ -685,7 +685,8 @@ __global__ void __launch_bounds__(kUThreads, TILES <= 4 ? 2 : 1) tiny_umma_kerne
 
     if (MODE == MODE_TRAIN) {
         if (t == 0) atomicAdd(a.fstate + FS_LOSS_STEP, loss_acc);
-        __threadfence();
+        // release: this CTA's gradient reductions are performed before its ticket becomes visible
+        asm volatile("fence.acq_rel.gpu;" ::: "memory");
         __syncthreads();
         if (t == 0) {
             const int tk = atomicAdd(a.ctrl + CTRL_TICKET, 1);
@@ -695,7 +696,7 @@ __global__ void __launch_bounds__(kUThreads, TILES <= 4 ? 2 : 1) tiny_umma_kerne
         TSTAMP(16);
         if (a.prof && threadIdx.x == 0) a.prof[64 + 2 * blockIdx.x + 1] = (long long)gtimer();
         if (*is_last) {
-            __threadfence(); TAILSTAMP(46); umma_sgd_tail(a, TinyLayout::total(C), reinterpret_cast<float*>(smem + S::OFF_PLANES));
+            asm volatile("fence.acq_rel.gpu;" ::: "memory"); TAILSTAMP(46); umma_sgd_tail(a, TinyLayout::total(C), reinterpret_cast<float*>(smem + S::OFF_PLANES));
             if (a.prof && threadIdx.x == 0) { a.prof[40] = (long long)gtimer(); a.prof[41] = blockIdx.x; }
         }
     }
