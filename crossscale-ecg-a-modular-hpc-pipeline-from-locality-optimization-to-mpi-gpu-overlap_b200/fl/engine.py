@@ -125,25 +125,7 @@ class TorchLocalTrainer:
         return loss_acc, n
 
 
-class _ScaledCE(torch.autograd.Function):
-    """mean cross entropy with the loss scale folded into the gradient (K5 kernel)."""
-
-    @staticmethod
-    def forward(ctx, logits, y, scale_t):
-        from ..ops import _lib
-        logits = logits.float().contiguous()
-        b, c = logits.shape
-        loss = torch.empty(1, dtype=torch.float32, device=logits.device)
-        dl = torch.empty_like(logits)
-        _lib.check(_lib.cuda_lib().cs_cross_entropy_fwd_bwd(logits.data_ptr(), y.data_ptr(), b, c, _lib.ptr(scale_t),
-                                                            loss.data_ptr(), dl.data_ptr(), _lib.stream_ptr()), "cs_cross_entropy")
-        ctx.save_for_backward(dl)
-        return loss[0]
-
-    @staticmethod
-    def backward(ctx, g):
-        (dl,) = ctx.saved_tensors
-        return dl * g, None, None
+from ..ops.ce_scaler import ScaledCrossEntropy as _ScaledCE  # noqa: E402
 
 
 class KernelLocalTrainer:
