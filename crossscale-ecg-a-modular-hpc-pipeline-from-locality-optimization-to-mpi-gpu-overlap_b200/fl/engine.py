@@ -146,6 +146,16 @@ class KernelLocalTrainer:
         self.fstate = torch.zeros(8, dtype=torch.float32, device=self.device)
         self.fstate[tk.FS_SCALE] = 65536.0 if use_scaler else 1.0
         self.loss_sum = torch.zeros((), dtype=torch.float32, device=self.device)
+        # bf16 shadow of the whole arena, refreshed by the SGD kernel: conv layers read their weights from it
+        # (no per-layer cast kernels) and accumulate weight gradients straight into the flat gradient arena
+        from ..ops.conv1d import Conv1dB200
+        self.shadow = self.flat.flat.to(torch.bfloat16)
+        for mod in model.modules():
+            if isinstance(mod, Conv1dB200) and mod.cin > 1:
+                i = next(j for j, q in enumerate(self.flat.params) if q is mod.weight)
+                off = self.flat.offsets[i]
+                mod.weight_bf16 = self.shadow[off:off + mod.weight.numel()].view_as(mod.weight)
+                mod.fused_wgrad = True
         self.sync = None
         if sync_grads:
             from ..parallel.grad_sync import GradSync
@@ -158,6 +168,11 @@ class KernelLocalTrainer:
     def load_flat(self, flat: torch.Tensor) -> None:
         if flat.data_ptr() != self.flat.flat.data_ptr():
             self.flat.flat.copy_(flat)
+        self.refresh_shadow()
+
+    def refresh_shadow(self) -> None:
+        """after the parameters changed outside the optimizer (aggregation, checkpoint load, arena rebind)"""
+        self.shadow.copy_(self.flat.flat)
 
     def step(self, x, y) -> torch.Tensor:
         self.model.train()
@@ -169,7 +184,7 @@ class KernelLocalTrainer:
         n = self.flat.flat.numel()
         self._lib.check(self._lib.cuda_lib().cs_sgd_momentum(
             self.flat.flat.data_ptr(), self.mom.data_ptr(), self.flat.grad.data_ptr(), n, self.lr, self.momentum, 0.0,
-            int(self.use_scaler), self.ctrl.data_ptr(), self.fstate.data_ptr(), 2.0, 0.5, 2000, None,
+            int(self.use_scaler), self.ctrl.data_ptr(), self.fstate.data_ptr(), 2.0, 0.5, 2000, self.shadow.data_ptr(),
             self._lib.stream_ptr()), "cs_sgd_momentum")
         self.launches += 1
         self.loss_sum += loss.detach()
@@ -338,6 +353,8 @@ class FedAvgRunner:
         if self.agg.inplace:                             # large model: parameters move into peer-mapped memory
             self.trainer.flat.rebind(self.agg.param_view)
             self.flat = self.trainer.flat.flat
+            if hasattr(self.trainer, "refresh_shadow"):
+                self.trainer.refresh_shadow()
             self.agg.set_weights(self.weight)
         self.prev = self.flat.clone()
         self.rows: List[dict] = []

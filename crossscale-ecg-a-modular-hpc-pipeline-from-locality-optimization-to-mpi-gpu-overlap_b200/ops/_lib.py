@@ -44,6 +44,9 @@ _CUDA_SIGS = {
     "cs_bn_apply": (i32, [vp, vp, vp, vp, vp, vp, vp, i64, i32, i32, vp]),
     "cs_bn_bwd_reduce": (i32, [vp, vp, vp, vp, vp, vp, vp, i64, i32, i32, vp]),
     "cs_bn_bwd_apply": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i64, i32, i32, vp]),
+    "cs_bn_finalize": (i32, [vp, vp, vp, vp, vp, i32, i64, f32, f32, vp]),
+    "cs_avgpool2_fwd": (i32, [vp, vp, i32, i32, i32, vp]),
+    "cs_avgpool2_bwd": (i32, [vp, vp, i32, i32, i32, vp]),
     "cs_avgpool_fwd": (i32, [vp, vp, i32, i32, i32, vp]),
     "cs_avgpool_bwd": (i32, [vp, vp, i32, i32, i32, vp]),
     "cs_ncl_f32_to_nlc_bf16": (i32, [vp, vp, i32, i32, i32, vp]),

@@ -16,40 +16,41 @@ from . import _lib
 
 class _BNAct(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, gamma, beta, residual, relu, eps, mean_in, var_in):
+    def forward(ctx, x, gamma, beta, residual, relu, eps, mean_in, var_in, running, momentum):
         lib, st = _lib.cuda_lib(), _lib.stream_ptr()
         x = x.contiguous()
         b, l, c = x.shape
         rows = b * l
-        if mean_in is None:                                # training: batch statistics
-            stats = torch.zeros(2 * c, dtype=torch.float32, device=x.device)
+        if mean_in is None:                                # training: batch statistics + running update, 2 launches
+            buf = torch.zeros(4 * c, dtype=torch.float32, device=x.device)
+            stats, mean, rstd = buf[:2 * c], buf[2 * c:3 * c], buf[3 * c:]
             _lib.check(lib.cs_bn_stats(x.data_ptr(), stats.data_ptr(), rows, c, st), "cs_bn_stats")
-            mean = stats[:c] / rows
-            var = (stats[c:] / rows - mean * mean).clamp_min_(0.0)
+            rm, rv = running if running is not None else (None, None)
+            _lib.check(lib.cs_bn_finalize(stats.data_ptr(), mean.data_ptr(), rstd.data_ptr(), _lib.ptr(rm), _lib.ptr(rv), c, rows,
+                                          float(eps), float(momentum), st), "cs_bn_finalize")
         else:
-            mean, var = mean_in.float(), var_in.float()
-        rstd = torch.rsqrt(var + eps)
+            mean = mean_in.float().contiguous()
+            rstd = torch.rsqrt(var_in.float() + eps)
         res = None if residual is None else residual.contiguous()
         y = torch.empty_like(x)
         g32, b32 = gamma.detach().float().contiguous(), beta.detach().float().contiguous()
         _lib.check(lib.cs_bn_apply(x.data_ptr(), _lib.ptr(res), y.data_ptr(), mean.contiguous().data_ptr(),
                                    rstd.contiguous().data_ptr(), g32.data_ptr(), b32.data_ptr(), rows, c, int(relu), st),
                    "cs_bn_apply")
-        ctx.save_for_backward(x, y, mean.contiguous(), rstd.contiguous(), g32)
+        ctx.save_for_backward(x, y, mean, rstd, g32)
         ctx.meta = (relu, residual is not None, mean_in is None)
-        ctx.mark_non_differentiable(mean, var)
-        return y, mean, var
+        return y
 
     @staticmethod
-    def backward(ctx, dy, _dm, _dv):
+    def backward(ctx, dy):
         x, y, mean, rstd, gamma = ctx.saved_tensors
         relu, has_res, training = ctx.meta
         lib, st = _lib.cuda_lib(), _lib.stream_ptr()
         b, l, c = x.shape
         rows = b * l
         dy = dy.contiguous()
-        dgamma = torch.zeros(c, dtype=torch.float32, device=x.device)
-        dbeta = torch.zeros(c, dtype=torch.float32, device=x.device)
+        dgb = torch.zeros(2 * c, dtype=torch.float32, device=x.device)
+        dgamma, dbeta = dgb[:c], dgb[c:]
         _lib.check(lib.cs_bn_bwd_reduce(x.data_ptr(), y.data_ptr(), dy.data_ptr(), mean.data_ptr(), rstd.data_ptr(),
                                         dgamma.data_ptr(), dbeta.data_ptr(), rows, c, int(relu), st), "cs_bn_bwd_reduce")
         dx = torch.empty_like(x)
@@ -60,7 +61,7 @@ class _BNAct(torch.autograd.Function):
         _lib.check(lib.cs_bn_bwd_apply(x.data_ptr(), y.data_ptr(), dy.data_ptr(), mean.data_ptr(), rstd.data_ptr(),
                                        gamma.data_ptr(), zg.data_ptr(), zb.data_ptr(), dx.data_ptr(), _lib.ptr(dres),
                                        rows, c, int(relu), st), "cs_bn_bwd_apply")
-        return dx, dgamma, dbeta, dres, None, None, None, None
+        return dx, dgamma, dbeta, dres, None, None, None, None, None, None
 
 
 class BNReLU1d(nn.Module):
@@ -82,14 +83,10 @@ class BNReLU1d(nn.Module):
                 y = y + residual
             return F.relu(y) if self.relu else y
         if self.training:
-            y, mean, var = _BNAct.apply(x, self.weight, self.bias, residual, self.relu, self.eps, None, None)
-            with torch.no_grad():
-                n = x.shape[0] * x.shape[1]
-                self.running_mean.lerp_(mean, self.momentum)
-                self.running_var.lerp_(var * (n / max(n - 1, 1)), self.momentum)
-            return y
-        y, _, _ = _BNAct.apply(x, self.weight, self.bias, residual, self.relu, self.eps, self.running_mean, self.running_var)
-        return y
+            return _BNAct.apply(x, self.weight, self.bias, residual, self.relu, self.eps, None, None,
+                                (self.running_mean, self.running_var), self.momentum)
+        return _BNAct.apply(x, self.weight, self.bias, residual, self.relu, self.eps, self.running_mean, self.running_var,
+                            None, self.momentum)
 
 
 class _GlobalAvgPool(torch.autograd.Function):
@@ -118,9 +115,27 @@ def global_avg_pool1d(x: torch.Tensor) -> torch.Tensor:
     return x.mean(dim=-1)
 
 
+class _AvgPool2(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        x = x.contiguous()
+        b, l, c = x.shape
+        y = torch.empty((b, l // 2, c), dtype=torch.bfloat16, device=x.device)
+        _lib.check(_lib.cuda_lib().cs_avgpool2_fwd(x.data_ptr(), y.data_ptr(), b, l, c, _lib.stream_ptr()), "cs_avgpool2_fwd")
+        ctx.shape = (b, l, c)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        b, l, c = ctx.shape
+        dx = torch.empty((b, l, c), dtype=torch.bfloat16, device=dy.device)
+        _lib.check(_lib.cuda_lib().cs_avgpool2_bwd(dy.contiguous().data_ptr(), dx.data_ptr(), b, l, c, _lib.stream_ptr()),
+                   "cs_avgpool2_bwd")
+        return dx
+
+
 def avg_pool2(x: torch.Tensor) -> torch.Tensor:
     """halve the length (mean of position pairs, odd tail dropped); layout-aware"""
     if x.is_cuda:
-        b, l, c = x.shape
-        return x[:, : (l // 2) * 2].reshape(b, l // 2, 2, c).float().mean(2).to(torch.bfloat16)
+        return _AvgPool2.apply(x)
     return F.avg_pool1d(x, 2)

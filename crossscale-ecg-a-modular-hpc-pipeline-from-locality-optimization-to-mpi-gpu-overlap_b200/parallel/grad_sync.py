@@ -69,7 +69,7 @@ class GradSync:
             j = self._owner[i]
             b = self.buckets[j]
             b["pending"] -= 1
-            if b["pending"] == 0:
+            if b["pending"] == 0 and not b.get("launched"):
                 self._launch(j)
         return hook
 
@@ -90,12 +90,15 @@ class GradSync:
                 dist.all_reduce(g)
                 g.mul_(1.0 / self.world)
         self.done_events[j].record(side)
+        b["launched"] = True
         self.launches += 1
 
     def finish(self) -> None:
         """Compute stream waits for every bucket; re-arms the hooks for the next backward."""
         cur = torch.cuda.current_stream()
         for j, b in enumerate(self.buckets):
-            if b["pending"] == 0:
+            if b.get("launched"):
                 cur.wait_event(self.done_events[j])
-            b["pending"] = len(b["members"])
+            elif b["pending"] != len(b["members"]):
+                raise RuntimeError(f"gradient bucket {j}: {b['pending']} of {len(b['members'])} gradients never arrived")
+            b["pending"], b["launched"] = len(b["members"]), False

@@ -45,6 +45,9 @@ int bn_apply(const void*, const void*, void*, const float*, const float*, const 
 int bn_bwd_reduce(const void*, const void*, const void*, const float*, const float*, float*, float*, int64_t, int, int, cudaStream_t);
 int bn_bwd_apply(const void*, const void*, const void*, const float*, const float*, const float*, const float*, const float*, void*, void*, int64_t, int, int, cudaStream_t);
 int avgpool_fwd(const void*, float*, int, int, int, cudaStream_t);
+int bn_finalize(const float*, float*, float*, float*, float*, int, int64_t, float, float, cudaStream_t);
+int avgpool2_fwd(const void*, void*, int, int, int, cudaStream_t);
+int avgpool2_bwd(const void*, void*, int, int, int, cudaStream_t);
 int avgpool_bwd(const float*, void*, int, int, int, cudaStream_t);
 int ncl_to_nlc(const float*, void*, int, int, int, cudaStream_t);
 int nlc_to_ncl(const void*, float*, int, int, int, cudaStream_t);
@@ -194,6 +197,12 @@ int cs_bn_bwd_apply(const void* x, const void* y, const void* dy, const float* m
                     int C, int relu, cs_stream_t s) {
     return bn_bwd_apply(x, y, dy, mean, rstd, gamma, dgamma, dbeta, dx, dres, rows, C, relu, ST(s));
 }
+int cs_bn_finalize(const float* stats, float* mean, float* rstd, float* running_mean, float* running_var, int C, int64_t rows,
+                   float eps, float momentum, cs_stream_t s) {
+    return bn_finalize(stats, mean, rstd, running_mean, running_var, C, rows, eps, momentum, ST(s));
+}
+int cs_avgpool2_fwd(const void* x, void* y, int B, int L, int C, cs_stream_t s) { return avgpool2_fwd(x, y, B, L, C, ST(s)); }
+int cs_avgpool2_bwd(const void* dy, void* dx, int B, int L, int C, cs_stream_t s) { return avgpool2_bwd(dy, dx, B, L, C, ST(s)); }
 int cs_avgpool_fwd(const void* x, float* out, int B, int L, int C, cs_stream_t s) { return avgpool_fwd(x, out, B, L, C, ST(s)); }
 int cs_avgpool_bwd(const float* dout, void* dx, int B, int L, int C, cs_stream_t s) { return avgpool_bwd(dout, dx, B, L, C, ST(s)); }
 int cs_ncl_f32_to_nlc_bf16(const float* x, void* y, int B, int C, int L, cs_stream_t s) { return ncl_to_nlc(x, y, B, C, L, ST(s)); }

@@ -240,17 +240,25 @@ int conv1d_fwd(const void* x, const void* w, const float* bias, void* y, int B, 
 }
 
 // w [K][Cout][Cin] -> wt [K][Cin][Cout] with taps flipped: wt[K-1-k][ci][co] = w[k][co][ci]
+// (32x32 shared-memory tile transpose per tap: coalesced reads and writes)
 __global__ void dgrad_weight_kernel(const __nv_bfloat16* __restrict__ w, __nv_bfloat16* __restrict__ wt, int K, int Cout, int Cin) {
-    const size_t total = (size_t)K * Cout * Cin;
-    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
-        const int ci = (int)(i % Cin), co = (int)((i / Cin) % Cout), k = (int)(i / ((size_t)Cin * Cout));
-        wt[((size_t)(K - 1 - k) * Cin + ci) * Cout + co] = w[i];
+    __shared__ __nv_bfloat16 tile[32][34];
+    const int k = blockIdx.z, co0 = blockIdx.y * 32, ci0 = blockIdx.x * 32;
+    const __nv_bfloat16* src = w + (size_t)k * Cout * Cin;
+    __nv_bfloat16* dst = wt + (size_t)(K - 1 - k) * Cin * Cout;
+    for (int j = threadIdx.y; j < 32; j += blockDim.y) {
+        const int co = co0 + j, ci = ci0 + threadIdx.x;
+        if (co < Cout && ci < Cin) tile[j][threadIdx.x] = src[(size_t)co * Cin + ci];
+    }
+    __syncthreads();
+    for (int j = threadIdx.y; j < 32; j += blockDim.y) {
+        const int ci = ci0 + j, co = co0 + threadIdx.x;
+        if (co < Cout && ci < Cin) dst[(size_t)ci * Cout + co] = tile[threadIdx.x][j];
     }
 }
 int conv1d_prepare_dgrad_weight(const void* w, void* wt, int K, int Cout, int Cin, cudaStream_t st) {
-    const size_t total = (size_t)K * Cout * Cin;
-    int blocks = (int)((total + 255) / 256); if (blocks > 1184) blocks = 1184;
-    dgrad_weight_kernel<<<blocks, 256, 0, st>>>((const __nv_bfloat16*)w, (__nv_bfloat16*)wt, K, Cout, Cin);
+    dim3 grid((Cin + 31) / 32, (Cout + 31) / 32, K), block(32, 8);
+    dgrad_weight_kernel<<<grid, block, 0, st>>>((const __nv_bfloat16*)w, (__nv_bfloat16*)wt, K, Cout, Cin);
     CS_CUDA_OK(cudaGetLastError());
     return CS_OK;
 }

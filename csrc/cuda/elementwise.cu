@@ -284,11 +284,10 @@ __global__ void bn_bwd_apply_kernel(const __nv_bfloat162* __restrict__ x, const 
 }
 
 static int rows_grid(int64_t rows, int rstep) {
-    int64_t want = (rows + rstep - 1) / rstep;
-    int64_t cap = (int64_t)num_sms() * 4;
-    // keep >= 64 rows per thread-row so the tail atomics stay rare
-    int64_t lim = (rows + 64LL * rstep - 1) / (64LL * rstep);
-    if (want > lim) want = lim;
+    // enough CTAs to fill the machine twice, but at least 8 rows per thread-row so the per-CTA tail
+    // (2*C atomics) stays small next to the streaming part
+    int64_t want = (rows + 8LL * rstep - 1) / (8LL * rstep);
+    const int64_t cap = (int64_t)num_sms() * 2;
     if (want > cap) want = cap;
     return (int)(want < 1 ? 1 : want);
 }
@@ -334,6 +333,64 @@ int bn_bwd_apply(const void* x, const void* y, const void* dy, const float* mean
     bn_bwd_apply_kernel<<<ew_grid(rows * (C / 2)), 256, 0, st>>>((const __nv_bfloat162*)x,
         (const __nv_bfloat162*)y, (const __nv_bfloat162*)dy, mean, rstd, gamma, dgamma, dbeta,
         (__nv_bfloat162*)dx, (__nv_bfloat162*)dres, rows, C, relu);
+    CS_CUDA_OK(cudaGetLastError());
+    return CS_OK;
+}
+
+// mean / rstd from the accumulated sums, plus the running-statistics update of nn.BatchNorm1d (momentum,
+// unbiased variance) — one tiny kernel instead of ~8 framework launches per layer
+__global__ void bn_finalize_kernel(const float* __restrict__ stats, float* __restrict__ mean, float* __restrict__ rstd,
+                                   float* __restrict__ running_mean, float* __restrict__ running_var, int C, float rows,
+                                   float eps, float momentum) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= C) return;
+    const float m = stats[c] / rows;
+    const float var = fmaxf(stats[C + c] / rows - m * m, 0.0f);
+    mean[c] = m;
+    rstd[c] = rsqrtf(var + eps);
+    if (running_mean) {
+        running_mean[c] += momentum * (m - running_mean[c]);
+        const float unbiased = var * (rows / fmaxf(rows - 1.0f, 1.0f));
+        running_var[c] += momentum * (unbiased - running_var[c]);
+    }
+}
+int bn_finalize(const float* stats, float* mean, float* rstd, float* rm, float* rv, int C, int64_t rows, float eps, float momentum,
+                cudaStream_t st) {
+    bn_finalize_kernel<<<(C + 127) / 128, 128, 0, st>>>(stats, mean, rstd, rm, rv, C, (float)rows, eps, momentum);
+    CS_CUDA_OK(cudaGetLastError());
+    return CS_OK;
+}
+
+// 2:1 average pooling along L of a channels-last bf16 tensor (odd tail dropped), and its backward
+__global__ void avgpool2_fwd_kernel(const __nv_bfloat162* __restrict__ x, __nv_bfloat162* __restrict__ y, int B, int L, int C) {
+    const int C2 = C >> 1, Lo = L >> 1;
+    const int64_t total = (int64_t)B * Lo * C2;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int cp = (int)(i % C2); const int64_t r = i / C2; const int lo = (int)(r % Lo); const int64_t b = r / Lo;
+        const __nv_bfloat162* src = x + ((b * L + 2 * lo) * C2 + cp);
+        const float2 a = __bfloat1622float2(src[0]), c = __bfloat1622float2(src[C2]);
+        y[i] = __floats2bfloat162_rn(0.5f * (a.x + c.x), 0.5f * (a.y + c.y));
+    }
+}
+__global__ void avgpool2_bwd_kernel(const __nv_bfloat162* __restrict__ dy, __nv_bfloat162* __restrict__ dx, int B, int L, int C) {
+    const int C2 = C >> 1, Lo = L >> 1;
+    const int64_t total = (int64_t)B * L * C2;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int cp = (int)(i % C2); const int64_t r = i / C2; const int l = (int)(r % L); const int64_t b = r / L;
+        float2 g = make_float2(0.f, 0.f);
+        if ((l >> 1) < Lo) { g = __bfloat1622float2(dy[(b * Lo + (l >> 1)) * C2 + cp]); g.x *= 0.5f; g.y *= 0.5f; }
+        dx[i] = __floats2bfloat162_rn(g.x, g.y);
+    }
+}
+int avgpool2_fwd(const void* x, void* y, int B, int L, int C, cudaStream_t st) {
+    CS_REQUIRE(C % 2 == 0 && L >= 2, "avgpool2: C must be even and L >= 2");
+    avgpool2_fwd_kernel<<<ew_grid((int64_t)B * (L / 2) * (C / 2)), 256, 0, st>>>((const __nv_bfloat162*)x, (__nv_bfloat162*)y, B, L, C);
+    CS_CUDA_OK(cudaGetLastError());
+    return CS_OK;
+}
+int avgpool2_bwd(const void* dy, void* dx, int B, int L, int C, cudaStream_t st) {
+    CS_REQUIRE(C % 2 == 0 && L >= 2, "avgpool2: C must be even and L >= 2");
+    avgpool2_bwd_kernel<<<ew_grid((int64_t)B * L * (C / 2)), 256, 0, st>>>((const __nv_bfloat162*)dy, (__nv_bfloat162*)dx, B, L, C);
     CS_CUDA_OK(cudaGetLastError());
     return CS_OK;
 }

@@ -165,6 +165,14 @@ int cs_bn_bwd_apply(const void* x, const void* y, const void* dy, const float* m
                     const float* rstd, const float* gamma, const float* dgamma,
                     const float* dbeta, void* dx, void* dres, int64_t rows, int C, int relu,
                     cs_stream_t stream);
+/* mean/rstd [C] from the stats of cs_bn_stats over `rows` rows; updates running_mean/var (may be NULL) like
+ * nn.BatchNorm1d (momentum, unbiased variance) */
+int cs_bn_finalize(const float* stats, float* mean, float* rstd, float* running_mean,
+                   float* running_var, int C, int64_t rows, float eps, float momentum,
+                   cs_stream_t stream);
+/* y[b,j,c] = (x[b,2j,c] + x[b,2j+1,c]) / 2, j < L/2 (bf16 channels-last); backward spreads dy/2 */
+int cs_avgpool2_fwd(const void* x, void* y, int B, int L, int C, cs_stream_t stream);
+int cs_avgpool2_bwd(const void* dy, void* dx, int B, int L, int C, cs_stream_t stream);
 /* out[b,c] = mean_l x[b,l,c]  (fp32 out);   backward: dx[b,l,c] = dout[b,c]/L */
 int cs_avgpool_fwd(const void* x, float* out, int B, int L, int C, cs_stream_t stream);
 int cs_avgpool_bwd(const float* dout, void* dx, int B, int L, int C, cs_stream_t stream);

@@ -32,7 +32,8 @@ def test_conv1d_fwd_dgrad_wgrad(B, L, Cin, Cout, K, pad):
     Lout = L + 2 * pad - K + 1
     assert y.shape == (B, Lout, Cout) and y.dtype == torch.bfloat16
     xr = x.detach().float().permute(0, 2, 1).contiguous().requires_grad_(True)              # [B,C,L] fp32 oracle
-    wr = m.weight.detach().clone().requires_grad_(True)
+    assert tuple(m.weight.shape) == (K, Cout, Cin)                                          # tap-major parameter
+    wr = m.weight_oik.detach().clone().contiguous().requires_grad_(True)                   # PyTorch [Cout,Cin,K] oracle
     br = m.bias.detach().clone().requires_grad_(True)
     yr = F.conv1d(xr, wr, br, padding=pad)
     assert _rel(y.float().permute(0, 2, 1), yr) < 1e-2
@@ -40,7 +41,7 @@ def test_conv1d_fwd_dgrad_wgrad(B, L, Cin, Cout, K, pad):
     y.backward(dy.to(torch.bfloat16))
     yr.backward(dy.permute(0, 2, 1))
     assert _rel(x.grad.float().permute(0, 2, 1), xr.grad) < 1e-2           # dgrad (bf16 output rounding)
-    assert _rel(m.weight.grad, wr.grad) < 5e-3                              # wgrad (fp32 output)
+    assert _rel(m.weight.grad.permute(1, 2, 0), wr.grad) < 5e-3             # wgrad (fp32 output)
     assert _rel(m.bias.grad, br.grad) < 5e-3
 
 
@@ -58,12 +59,12 @@ def test_conv1d_relu_epilogue_and_cin1():
     m = Conv1dB200(1, 64, 7, padding=3, bias=True).to(DEV)
     xin = torch.randn(6, 1, 500, device=DEV)
     out = m(xin)
-    wr, br = m.weight.detach().clone().requires_grad_(True), m.bias.detach().clone().requires_grad_(True)
+    wr, br = m.weight_oik.detach().clone().contiguous().requires_grad_(True), m.bias.detach().clone().requires_grad_(True)
     ref = F.conv1d(xin, wr, br, padding=3)
     assert out.shape == (6, 500, 64) and _rel(out.float().permute(0, 2, 1), ref) < 1e-2
     dy = _bf(torch.randn(6, 500, 64, device=DEV))
     out.backward(dy.to(torch.bfloat16)); ref.backward(dy.permute(0, 2, 1))
-    assert _rel(m.weight.grad, wr.grad) < 1e-3 and _rel(m.bias.grad, br.grad) < 1e-3
+    assert _rel(m.weight.grad.permute(1, 2, 0), wr.grad) < 1e-3 and _rel(m.bias.grad, br.grad) < 1e-3
 
 
 @pytest.mark.parametrize("relu,with_res", [(True, False), (True, True), (False, False)])
@@ -105,6 +106,13 @@ def test_pool_and_layout_kernels():
     torch.testing.assert_close(p, x.detach().float().mean(1), rtol=1e-4, atol=1e-5)
     p.backward(torch.ones_like(p))
     torch.testing.assert_close(x.grad.float(), torch.full_like(x.grad.float(), _bf(torch.tensor(1 / 123)).item()), rtol=1e-2, atol=1e-4)
+    from crossscale.ops.norm_act import avg_pool2
+    z = _bf(torch.randn(3, 91, 32, device=DEV)).to(torch.bfloat16).requires_grad_(True)
+    q = avg_pool2(z)
+    ref = F.avg_pool1d(z.detach().float().permute(0, 2, 1), 2).permute(0, 2, 1)
+    assert q.shape == (3, 45, 32) and _rel(q.float(), ref) < 1e-2
+    q.backward(torch.ones_like(q))
+    assert float(z.grad[:, :90].float().mean()) == 0.5 and float(z.grad[:, 90].float().abs().max()) == 0.0
     lib = _lib.cuda_lib()
     a = torch.randn(3, 40, 77, device=DEV)
     nlc = torch.empty(3, 77, 40, dtype=torch.bfloat16, device=DEV)

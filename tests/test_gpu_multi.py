@@ -117,6 +117,7 @@ for step in range(5):
     loss.backward()
     dist.all_reduce(tr2.flat.grad); tr2.flat.grad.mul_(1.0 / world)
     tr2.mom.mul_(0.9).add_(tr2.flat.grad); tr2.flat.flat.add_(tr2.mom, alpha=-5e-2)
+    tr2.refresh_shadow()                                 # conv layers read their weights from the bf16 shadow
 err = float((flat - tr2.flat.flat).abs().max() / (tr2.flat.flat.abs().max()))
 if rank == 0:
     print("RESULT " + json.dumps({"identical": ident, "rel_err_vs_nccl": err, "status": tr.sync.comm.status(),
