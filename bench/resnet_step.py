@@ -75,6 +75,11 @@ def main():
     y = torch.randint(0, 5, (a.batch,), device=dev)
     ours = KernelLocalTrainer(resnet1d_wide_25m(5).to(dev), dev)
     t_ours = timed(lambda: ours.step(x, y), a.steps)
+    graphed = KernelLocalTrainer(resnet1d_wide_25m(5).to(dev), dev, use_graph=True)
+    for _ in range(5):
+        graphed.step(x, y)
+    t_graph = timed(lambda: graphed.step(x, y), a.steps)
+    l0 = float(graphed.step(x, y)); [graphed.step(x, y) for _ in range(20)]; l1 = float(graphed.step(x, y))
     stock = StockResNet().to(dev)
     opt = torch.optim.SGD(stock.parameters(), lr=1e-2, momentum=0.9)
 
@@ -87,6 +92,8 @@ def main():
 
     t_stock = timed(stock_step, a.steps)
     stock_cl = StockResNet().to(dev)
+    print(f"   whole-step CUDA graph: {t_graph:.2f} ms/step ({a.batch / t_graph * 1e3:,.0f} samples/s), x{t_stock / t_graph:.2f} vs stock; "
+          f"loss {l0:.4f} -> {l1:.4f} after 20 more graphed steps")
     print(f"ResNet-1D wide, B={a.batch} L={a.L}: ours {t_ours:.2f} ms/step ({a.batch / t_ours * 1e3:,.0f} samples/s) | "
           f"stock PyTorch/cuDNN bf16 autocast {t_stock:.2f} ms/step ({a.batch / t_stock * 1e3:,.0f} samples/s) | x{t_stock / t_ours:.2f}")
 

@@ -135,7 +135,7 @@ class KernelLocalTrainer:
     ``sync_grads`` the gradient buckets are all-reduced in-kernel over NVLink while backward runs."""
 
     def __init__(self, model: torch.nn.Module, device, lr=1e-2, momentum=0.9, use_scaler: bool = False,
-                 sync_grads: bool = False, bucket_bytes: int = 4 << 20, wire: str = "fp32"):
+                 sync_grads: bool = False, bucket_bytes: int = 4 << 20, wire: str = "fp32", use_graph: bool = False):
         from ..models.tiny_ecg import FlatParams
         from ..ops import _lib
         self.model, self.device, self._lib = model, torch.device(device), _lib
@@ -161,6 +161,8 @@ class KernelLocalTrainer:
             from ..parallel.grad_sync import GradSync
             self.sync = GradSync(self.flat, bucket_bytes=bucket_bytes, wire=wire)
         self.launches = 0
+        # whole-step CUDA graph (forward + backward + bucket all-reduces + SGD): ~600 launches become one replay
+        self.use_graph, self._graph, self._warm = bool(use_graph), None, 0
 
     def flat_parameters(self) -> torch.Tensor:
         return self.flat.flat
@@ -175,6 +177,23 @@ class KernelLocalTrainer:
         self.shadow.copy_(self.flat.flat)
 
     def step(self, x, y) -> torch.Tensor:
+        if not self.use_graph:
+            return self._step(x, y)
+        if self._graph is None:
+            if self._warm < 3:                              # eager warm-up: kernel attributes, allocator pools
+                self._warm += 1
+                return self._step(x, y)
+            self._sx, self._sy = x.clone(), y.clone()
+            torch.cuda.synchronize()
+            self._graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self._graph):
+                self._sloss = self._step(self._sx, self._sy)
+        self._sx.copy_(x)
+        self._sy.copy_(y)
+        self._graph.replay()
+        return self._sloss
+
+    def _step(self, x, y) -> torch.Tensor:
         self.model.train()
         self.flat.grad.zero_()
         loss = _ScaledCE.apply(self.model(x), y, self.fstate[tk.FS_SCALE:tk.FS_SCALE + 1] if self.use_scaler else None)
@@ -335,7 +354,7 @@ class FedAvgRunner:
             self.kernel_generic = (self.device.type == "cuda" and tk.use_kernels() and not isinstance(model, TinyECG))
             if self.kernel_generic:
                 self.trainer = KernelLocalTrainer(model, self.device, lr, momentum, use_scaler=(amp == "fp16"),
-                                                  sync_grads=sync_grads)
+                                                  sync_grads=sync_grads, use_graph=use_graph)
                 self.mom = self.trainer.mom
             else:
                 self.trainer = TorchLocalTrainer(model, self.device, lr, momentum,

@@ -164,6 +164,24 @@ def test_kernel_trainer_resnet_small_learns_and_grad_sync_single_rank():
             assert tr.sync.comm.status() == 0
 
 
+def test_kernel_trainer_whole_step_graph_matches_eager():
+    import copy
+    from crossscale.fl.engine import KernelLocalTrainer
+    from crossscale.models.resnet1d_wide import resnet1d_small
+    torch.manual_seed(1)
+    base = resnet1d_small(5).to(DEV)
+    xs = [torch.randn(32, 1, 360, device=DEV) for _ in range(8)]
+    ys = [torch.randint(0, 5, (32,), device=DEV) for _ in range(8)]
+    outs = []
+    for graph in (False, True):
+        tr = KernelLocalTrainer(copy.deepcopy(base), DEV, lr=2e-2, use_graph=graph)
+        losses = [float(tr.step(x, y)) for x, y in zip(xs, ys)]
+        outs.append((tr.flat.flat.clone(), losses))
+        assert (tr._graph is not None) == graph
+    assert _rel(outs[1][0], outs[0][0]) < 2e-2                      # atomics order differs: not bit-exact
+    assert all(abs(a - b) < 0.05 for a, b in zip(outs[0][1], outs[1][1]))
+
+
 def test_fedavg_runner_with_resnet_small(synth_shards=None):
     import glob, os, tempfile
     from crossscale.data.shard_dataset import load_shards_to_gpu

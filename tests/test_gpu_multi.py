@@ -97,7 +97,8 @@ rank, world, lr = launch.init_distributed()
 dev = torch.device("cuda", lr); torch.cuda.set_device(dev)
 torch.manual_seed(0)                                   # identical initial model on every rank
 model = resnet1d_small(5).to(dev)
-tr = KernelLocalTrainer(model, dev, lr=5e-2, sync_grads=True, bucket_bytes=8 << 10)
+tr = KernelLocalTrainer(model, dev, lr=5e-2, sync_grads=True, bucket_bytes=8 << 10,
+                        use_graph=os.environ.get("CS_TEST_GRAPH") == "1")
 x, y = make_mitbih_like_beats(256, 360, 5, seed=100 + rank)   # different data per rank
 x, y = torch.from_numpy(x).to(dev).unsqueeze(1), torch.from_numpy(y).to(dev)
 for step in range(5):
@@ -126,10 +127,12 @@ launch.shutdown()
 '''
 
 
-def test_grad_sync_two_gpus(tmp_path):
+@pytest.mark.parametrize("graph", ["0", "1"])
+def test_grad_sync_two_gpus(tmp_path, graph, monkeypatch):
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
-    r = _run(2, GRAD_WORKER, tmp_path, 29741)
+    monkeypatch.setenv("CS_TEST_GRAPH", graph)             # "1": forward+backward+bucket all-reduces+SGD in one CUDA graph
+    r = _run(2, GRAD_WORKER, tmp_path, 29741 + int(graph))
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     res = json.loads([l for l in r.stdout.splitlines() if l.startswith("RESULT ")][-1][7:])
     assert res["identical"] and res["status"] == 0 and res["buckets"] >= 2 and res["rel_err_vs_nccl"] < 2e-2, res
