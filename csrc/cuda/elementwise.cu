@@ -204,101 +204,160 @@ int zscore_rows(const float* x, void* y, int B, int L, int out_bf16, cudaStream_
 }
 
 // ------------------------------------------------------------------------------------------------
-// K4 BN / ReLU / residual / pool on channels-last bf16 [rows, C]
-// Thread t owns channel pair (t % (C/2)) and strides over rows -> coalesced 4-byte accesses,
-// per-thread fp32 accumulators, one atomic per (block, channel) at the end.
+// K4 BN / ReLU / residual / pool on channels-last bf16 [rows, C], C % 8 == 0.
+// Every thread moves 16 bytes (8 channels) per access.  Reductions: a thread owns one 8-channel group and
+// strides over rows with 4 independent loads in flight, partial sums meet in shared memory, and each CTA
+// finishes with ONE atomic per channel and quantity (<= 148 CTAs, so the atomic tail stays short).
 // ------------------------------------------------------------------------------------------------
-__global__ void bn_stats_kernel(const __nv_bfloat162* __restrict__ x, float* __restrict__ stats, int64_t rows, int C) {
-    const int C2 = C >> 1;
-    const int cp = threadIdx.x % C2;
-    const int rlane = threadIdx.x / C2, rstep = blockDim.x / C2;
-    if (rlane >= rstep) return;
-    float s0 = 0, s1 = 0, q0 = 0, q1 = 0;
-    for (int64_t r = (int64_t)blockIdx.x * rstep + rlane; r < rows; r += (int64_t)gridDim.x * rstep) {
-        float2 v = __bfloat1622float2(x[r * C2 + cp]);
-        s0 += v.x; s1 += v.y; q0 = fmaf(v.x, v.x, q0); q1 = fmaf(v.y, v.y, q1);
-    }
-    atomicAdd(stats + 2 * cp, s0); atomicAdd(stats + 2 * cp + 1, s1);
-    atomicAdd(stats + C + 2 * cp, q0); atomicAdd(stats + C + 2 * cp + 1, q1);
+struct bf16x8 { uint4 v; };
+__device__ __forceinline__ void unpack8(const uint4& u, float (&f)[8]) {
+    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { const float2 t = __bfloat1622float2(h[i]); f[2 * i] = t.x; f[2 * i + 1] = t.y; }
+}
+__device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
+    uint4 u;
+    __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&u);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+    return u;
 }
 
-__global__ void bn_apply_kernel(const __nv_bfloat162* __restrict__ x, const __nv_bfloat162* __restrict__ res,
-                                __nv_bfloat162* __restrict__ y, const float* __restrict__ mean,
-                                const float* __restrict__ rstd, const float* __restrict__ gamma,
+constexpr int kRedThreads = 256;
+
+// block-level finish of a column reduction: acc[Q][8] per thread -> atomics on out[q*C + channel]
+// (called by ALL threads of the block; threads with rl >= rpb hold no partials)
+template <int Q>
+__device__ __forceinline__ void column_reduce_finish(float (&acc)[Q][8], float* const (&out)[Q], int C, int g, int rl, int rpb,
+                                                     float* sm /* [rpb][Q][C] */) {
+    if (rl < rpb) {
+#pragma unroll
+        for (int q = 0; q < Q; ++q)
+#pragma unroll
+            for (int j = 0; j < 8; ++j) sm[((size_t)rl * Q + q) * C + g * 8 + j] = acc[q][j];
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < Q * C; i += blockDim.x) {
+        float s = 0.0f;
+        for (int r = 0; r < rpb; ++r) s += sm[(size_t)r * Q * C + i];
+        atomicAdd(out[i / C] + (i % C), s);
+    }
+}
+
+__global__ void __launch_bounds__(kRedThreads) bn_stats_kernel(const uint4* __restrict__ x, float* __restrict__ stats, int64_t rows, int C) {
+    extern __shared__ float sm_red[];
+    const int G = C >> 3, rpb = kRedThreads / G;
+    const int g = threadIdx.x % G, rl = threadIdx.x / G;
+    float acc[2][8] = {};
+    if (rl < rpb) {
+        const int64_t stride = (int64_t)gridDim.x * rpb;
+        for (int64_t r = (int64_t)blockIdx.x * rpb + rl; r < rows; r += 4 * stride) {
+            uint4 v[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) { const int64_t rr = r + u * stride; if (rr < rows) v[u] = __ldg(x + rr * G + g); }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                if (r + u * stride < rows) {
+                    float f[8]; unpack8(v[u], f);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) { acc[0][j] += f[j]; acc[1][j] = fmaf(f[j], f[j], acc[1][j]); }
+                }
+            }
+        }
+    }
+    float* const out[2] = {stats, stats + C};
+    column_reduce_finish<2>(acc, out, C, g, rl, rpb, sm_red);
+}
+
+__global__ void bn_apply_kernel(const uint4* __restrict__ x, const uint4* __restrict__ res, uint4* __restrict__ y,
+                                const float* __restrict__ mean, const float* __restrict__ rstd, const float* __restrict__ gamma,
                                 const float* __restrict__ beta, int64_t rows, int C, int relu) {
-    const int C2 = C >> 1;
-    const int64_t total = rows * C2;
+    const int G = C >> 3;
+    const int64_t total = rows * G;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-        const int c = (int)(i % C2) * 2;
-        float2 v = __bfloat1622float2(x[i]);
-        float a0 = rstd[c] * gamma[c], a1 = rstd[c + 1] * gamma[c + 1];
-        float o0 = (v.x - mean[c]) * a0 + beta[c], o1 = (v.y - mean[c + 1]) * a1 + beta[c + 1];
-        if (res) { float2 r = __bfloat1622float2(res[i]); o0 += r.x; o1 += r.y; }
-        if (relu) { o0 = fmaxf(o0, 0.0f); o1 = fmaxf(o1, 0.0f); }
-        y[i] = __floats2bfloat162_rn(o0, o1);
+        const int c = (int)(i % G) * 8;
+        float f[8], r[8];
+        unpack8(__ldg(x + i), f);
+        if (res) unpack8(__ldg(res + i), r);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            float o = (f[j] - mean[c + j]) * (rstd[c + j] * gamma[c + j]) + beta[c + j];
+            if (res) o += r[j];
+            f[j] = relu ? fmaxf(o, 0.0f) : o;
+        }
+        y[i] = pack8(f);
     }
 }
 
-__global__ void bn_bwd_reduce_kernel(const __nv_bfloat162* __restrict__ x, const __nv_bfloat162* __restrict__ y,
-                                     const __nv_bfloat162* __restrict__ dy, const float* __restrict__ mean,
-                                     const float* __restrict__ rstd, float* __restrict__ dgamma,
-                                     float* __restrict__ dbeta, int64_t rows, int C, int relu) {
-    const int C2 = C >> 1;
-    const int cp = threadIdx.x % C2;
-    const int rlane = threadIdx.x / C2, rstep = blockDim.x / C2;
-    if (rlane >= rstep) return;
-    const int c = 2 * cp;
-    const float m0 = mean[c], m1 = mean[c + 1], r0 = rstd[c], r1 = rstd[c + 1];
-    float g0 = 0, g1 = 0, b0 = 0, b1 = 0;
-    for (int64_t r = (int64_t)blockIdx.x * rstep + rlane; r < rows; r += (int64_t)gridDim.x * rstep) {
-        float2 d = __bfloat1622float2(dy[r * C2 + cp]);
-        if (relu) { float2 o = __bfloat1622float2(y[r * C2 + cp]); if (o.x <= 0.0f) d.x = 0.0f; if (o.y <= 0.0f) d.y = 0.0f; }
-        float2 v = __bfloat1622float2(x[r * C2 + cp]);
-        g0 = fmaf(d.x, (v.x - m0) * r0, g0); g1 = fmaf(d.y, (v.y - m1) * r1, g1);
-        b0 += d.x; b1 += d.y;
+__global__ void __launch_bounds__(kRedThreads) bn_bwd_reduce_kernel(const uint4* __restrict__ x, const uint4* __restrict__ y,
+                                                                    const uint4* __restrict__ dy, const float* __restrict__ mean,
+                                                                    const float* __restrict__ rstd, float* __restrict__ dgamma,
+                                                                    float* __restrict__ dbeta, int64_t rows, int C, int relu) {
+    extern __shared__ float sm_red[];
+    const int G = C >> 3, rpb = kRedThreads / G;
+    const int g = threadIdx.x % G, rl = threadIdx.x / G;
+    float acc[2][8] = {};
+    if (rl < rpb) {
+        float m[8], rs[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { m[j] = mean[g * 8 + j]; rs[j] = rstd[g * 8 + j]; }
+        const int64_t stride = (int64_t)gridDim.x * rpb;
+        for (int64_t r = (int64_t)blockIdx.x * rpb + rl; r < rows; r += 2 * stride) {
+            uint4 vx[2], vy[2], vd[2];
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+                const int64_t rr = r + u * stride;
+                if (rr < rows) { vx[u] = __ldg(x + rr * G + g); vd[u] = __ldg(dy + rr * G + g); if (relu) vy[u] = __ldg(y + rr * G + g); }
+            }
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+                if (r + u * stride < rows) {
+                    float fx[8], fd[8], fy[8];
+                    unpack8(vx[u], fx); unpack8(vd[u], fd);
+                    if (relu) unpack8(vy[u], fy);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        const float d = (relu && fy[j] <= 0.0f) ? 0.0f : fd[j];
+                        acc[0][j] = fmaf(d, (fx[j] - m[j]) * rs[j], acc[0][j]);
+                        acc[1][j] += d;
+                    }
+                }
+            }
+        }
     }
-    atomicAdd(dgamma + c, g0); atomicAdd(dgamma + c + 1, g1);
-    atomicAdd(dbeta + c, b0); atomicAdd(dbeta + c + 1, b1);
+    float* const out[2] = {dgamma, dbeta};
+    column_reduce_finish<2>(acc, out, C, g, rl, rpb, sm_red);
 }
 
-__global__ void bn_bwd_apply_kernel(const __nv_bfloat162* __restrict__ x, const __nv_bfloat162* __restrict__ y,
-                                    const __nv_bfloat162* __restrict__ dy, const float* __restrict__ mean,
-                                    const float* __restrict__ rstd, const float* __restrict__ gamma,
-                                    const float* __restrict__ dgamma, const float* __restrict__ dbeta,
-                                    __nv_bfloat162* __restrict__ dx, __nv_bfloat162* __restrict__ dres,
-                                    int64_t rows, int C, int relu) {
-    const int C2 = C >> 1;
-    const int64_t total = rows * C2;
+__global__ void bn_bwd_apply_kernel(const uint4* __restrict__ x, const uint4* __restrict__ y, const uint4* __restrict__ dy,
+                                    const float* __restrict__ mean, const float* __restrict__ rstd, const float* __restrict__ gamma,
+                                    const float* __restrict__ dgamma, const float* __restrict__ dbeta, uint4* __restrict__ dx,
+                                    uint4* __restrict__ dres, int64_t rows, int C, int relu) {
+    const int G = C >> 3;
+    const int64_t total = rows * G;
     const float invn = 1.0f / (float)rows;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-        const int c = (int)(i % C2) * 2;
-        float2 d = __bfloat1622float2(dy[i]);
-        if (relu) { float2 o = __bfloat1622float2(y[i]); if (o.x <= 0.0f) d.x = 0.0f; if (o.y <= 0.0f) d.y = 0.0f; }
-        if (dres) dres[i] = __floats2bfloat162_rn(d.x, d.y);
-        float2 v = __bfloat1622float2(x[i]);
-        float xh0 = (v.x - mean[c]) * rstd[c], xh1 = (v.y - mean[c + 1]) * rstd[c + 1];
-        float o0 = gamma[c] * rstd[c] * (d.x - invn * (dbeta[c] + xh0 * dgamma[c]));
-        float o1 = gamma[c + 1] * rstd[c + 1] * (d.y - invn * (dbeta[c + 1] + xh1 * dgamma[c + 1]));
-        dx[i] = __floats2bfloat162_rn(o0, o1);
+        const int c = (int)(i % G) * 8;
+        float fx[8], fd[8], fy[8];
+        unpack8(__ldg(x + i), fx); unpack8(__ldg(dy + i), fd);
+        if (relu) unpack8(__ldg(y + i), fy);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) if (relu && fy[j] <= 0.0f) fd[j] = 0.0f;
+        if (dres) dres[i] = pack8(fd);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const float xh = (fx[j] - mean[c + j]) * rstd[c + j];
+            fx[j] = gamma[c + j] * rstd[c + j] * (fd[j] - invn * (dbeta[c + j] + xh * dgamma[c + j]));
+        }
+        dx[i] = pack8(fx);
     }
 }
 
-static int rows_grid(int64_t rows, int rstep) {
-    // enough CTAs to fill the machine twice, but at least 8 rows per thread-row so the per-CTA tail
-    // (2*C atomics) stays small next to the streaming part
-    int64_t want = (rows + 8LL * rstep - 1) / (8LL * rstep);
-    const int64_t cap = (int64_t)num_sms() * 2;
+static int red_grid(int64_t rows, int rpb, int unroll) {
+    int64_t want = (rows + (int64_t)rpb * unroll * 4 - 1) / ((int64_t)rpb * unroll * 4);   // >= 4 passes per thread
+    const int64_t cap = num_sms();
     if (want > cap) want = cap;
     return (int)(want < 1 ? 1 : want);
-}
-
-int bn_stats(const void* x, float* stats, int64_t rows, int C, cudaStream_t st) {
-    CS_REQUIRE(C >= 2 && C % 2 == 0 && C <= 2048, "bn_stats: C=%d must be even and <= 2048", C);
-    int threads = 1024; int rstep = threads / (C / 2);
-    if (rstep < 1) { threads = C / 2; rstep = 1; }
-    bn_stats_kernel<<<rows_grid(rows, rstep), threads, 0, st>>>((const __nv_bfloat162*)x, stats, rows, C);
-    CS_CUDA_OK(cudaGetLastError());
-    return CS_OK;
 }
 
 static int ew_grid(int64_t total) {
@@ -306,22 +365,31 @@ static int ew_grid(int64_t total) {
     return (int)(want < 1 ? 1 : (want > cap ? cap : want));
 }
 
+int bn_stats(const void* x, float* stats, int64_t rows, int C, cudaStream_t st) {
+    CS_REQUIRE(C >= 8 && C % 8 == 0 && C <= 2048, "bn_stats: C=%d must be a multiple of 8 and <= 2048", C);
+    const int rpb = kRedThreads / (C / 8);
+    const size_t smem = (size_t)rpb * 2 * C * sizeof(float);
+    bn_stats_kernel<<<red_grid(rows, rpb, 4), kRedThreads, smem, st>>>((const uint4*)x, stats, rows, C);
+    CS_CUDA_OK(cudaGetLastError());
+    return CS_OK;
+}
+
 int bn_apply(const void* x, const void* res, void* y, const float* mean, const float* rstd,
              const float* gamma, const float* beta, int64_t rows, int C, int relu, cudaStream_t st) {
-    CS_REQUIRE(C >= 2 && C % 2 == 0, "bn_apply: C must be even");
-    bn_apply_kernel<<<ew_grid(rows * (C / 2)), 256, 0, st>>>((const __nv_bfloat162*)x, (const __nv_bfloat162*)res,
-        (__nv_bfloat162*)y, mean, rstd, gamma, beta, rows, C, relu);
+    CS_REQUIRE(C >= 8 && C % 8 == 0, "bn_apply: C must be a multiple of 8");
+    bn_apply_kernel<<<ew_grid(rows * (C / 8)), 256, 0, st>>>((const uint4*)x, (const uint4*)res, (uint4*)y, mean, rstd, gamma, beta,
+                                                              rows, C, relu);
     CS_CUDA_OK(cudaGetLastError());
     return CS_OK;
 }
 
 int bn_bwd_reduce(const void* x, const void* y, const void* dy, const float* mean, const float* rstd,
                   float* dgamma, float* dbeta, int64_t rows, int C, int relu, cudaStream_t st) {
-    CS_REQUIRE(C >= 2 && C % 2 == 0 && C <= 2048, "bn_bwd: C=%d must be even and <= 2048", C);
-    int threads = 1024; int rstep = threads / (C / 2);
-    if (rstep < 1) { threads = C / 2; rstep = 1; }
-    bn_bwd_reduce_kernel<<<rows_grid(rows, rstep), threads, 0, st>>>((const __nv_bfloat162*)x,
-        (const __nv_bfloat162*)y, (const __nv_bfloat162*)dy, mean, rstd, dgamma, dbeta, rows, C, relu);
+    CS_REQUIRE(C >= 8 && C % 8 == 0 && C <= 2048, "bn_bwd: C=%d must be a multiple of 8 and <= 2048", C);
+    const int rpb = kRedThreads / (C / 8);
+    const size_t smem = (size_t)rpb * 2 * C * sizeof(float);
+    bn_bwd_reduce_kernel<<<red_grid(rows, rpb, 2), kRedThreads, smem, st>>>((const uint4*)x, (const uint4*)y, (const uint4*)dy, mean,
+                                                                            rstd, dgamma, dbeta, rows, C, relu);
     CS_CUDA_OK(cudaGetLastError());
     return CS_OK;
 }
@@ -329,10 +397,9 @@ int bn_bwd_reduce(const void* x, const void* y, const void* dy, const float* mea
 int bn_bwd_apply(const void* x, const void* y, const void* dy, const float* mean, const float* rstd,
                  const float* gamma, const float* dgamma, const float* dbeta, void* dx, void* dres,
                  int64_t rows, int C, int relu, cudaStream_t st) {
-    CS_REQUIRE(C >= 2 && C % 2 == 0, "bn_bwd: C must be even");
-    bn_bwd_apply_kernel<<<ew_grid(rows * (C / 2)), 256, 0, st>>>((const __nv_bfloat162*)x,
-        (const __nv_bfloat162*)y, (const __nv_bfloat162*)dy, mean, rstd, gamma, dgamma, dbeta,
-        (__nv_bfloat162*)dx, (__nv_bfloat162*)dres, rows, C, relu);
+    CS_REQUIRE(C >= 8 && C % 8 == 0, "bn_bwd: C must be a multiple of 8");
+    bn_bwd_apply_kernel<<<ew_grid(rows * (C / 8)), 256, 0, st>>>((const uint4*)x, (const uint4*)y, (const uint4*)dy, mean, rstd, gamma,
+                                                                  dgamma, dbeta, (uint4*)dx, (uint4*)dres, rows, C, relu);
     CS_CUDA_OK(cudaGetLastError());
     return CS_OK;
 }

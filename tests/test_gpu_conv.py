@@ -67,11 +67,11 @@ def test_conv1d_relu_epilogue_and_cin1():
     assert _rel(m.weight.grad.permute(1, 2, 0), wr.grad) < 1e-3 and _rel(m.bias.grad, br.grad) < 1e-3
 
 
-@pytest.mark.parametrize("relu,with_res", [(True, False), (True, True), (False, False)])
-def test_bn_relu_residual_kernels(relu, with_res):
+@pytest.mark.parametrize("relu,with_res,C", [(True, False, 64), (True, True, 64), (False, False, 64), (True, True, 768), (True, False, 16)])
+def test_bn_relu_residual_kernels(relu, with_res, C):
     from crossscale.ops.norm_act import BNReLU1d
     torch.manual_seed(3)
-    B, L, C = 8, 250, 64
+    B, L = 8, 250
     bn = BNReLU1d(C, relu=relu).to(DEV)
     with torch.no_grad():
         bn.weight.copy_(torch.rand(C, device=DEV) + 0.5); bn.bias.copy_(torch.randn(C, device=DEV) * 0.1)
