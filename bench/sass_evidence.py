@@ -9,9 +9,11 @@ REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(REPO, "lib", "libcrossscale_cuda.so")
 OUT = os.path.join(REPO, "profiles", "sass")
 KERNELS = ["tiny_umma_kernelILi4ELb0ELi2E", "tiny_umma_kernelILi4ELb1ELi2E", "tiny_ecg_f32_kernelILi2E", "conv1d_fwd_kernel",
-           "conv1d_wgrad_kernel", "fedavg_oneshot_kernelILb0E", "fedavg_twoshot_kernelILb0E", "fedavg_twoshot_kernelILb1E"]
+           "conv1d_wgrad_kernel", "fedavg_oneshot_kernelILb0E", "fedavg_twoshot_kernelILb0E", "fedavg_twoshot_kernelILb1E",
+           "fedavg_inplace_kernel", "fedavg_nvls_kernel", "barrier_kernel", "bn_stats_kernel", "bn_bwd_reduce_kernel",
+           "sgd_momentum_kernel", "gather_rows_kernel", "ce_fwd_bwd_kernel", "cin1_fwd_kernel", "cin1_wgrad_kernel"]
 MN = re.compile(r"^\s+/\*[0-9a-f]{4,5}\*/\s+(?:@!?U?P\d+\s+)?([A-Za-z0-9_.]+)")
-KEEP = re.compile(r"UTC|LDTM|STTM|UTMA|SYNCS|REDG|ATOMG|MEMBAR|ERRBAR|ELECT|ACQBULK|UBLKCP|FFMA$|HMMA|.*\.SYS")
+KEEP = re.compile(r"UTC|LDTM|STTM|UTMA|SYNCS|REDG|ATOMG|MEMBAR|ERRBAR|ELECT|ACQBULK|UBLKCP|FFMA$|HMMA|LDGMC|STG.*MMEM|.*\.SYS|LDG\.E\.128|STG\.E\.128")
 
 HEAD = """# SASS evidence (`cuobjdump -sass lib/libcrossscale_cuda.so`, sm_100a)
 
@@ -19,7 +21,8 @@ Histogram of the tensor-core / TMA / TMEM / NVLink-relevant mnemonics per kernel
 `UTCHMMA` = tcgen05.mma kind::f16, `LDTM` = tcgen05.ld, `UTCBAR` = tcgen05.commit, `UTCATOMSWS` = tcgen05.alloc/dealloc,
 `UTMALDG.4D` = cp.async.bulk.tensor.4d (TMA), `SYNCS.*` = mbarrier, `REDG.E.ADD.F32x4` = red.global.add.v4.f32,
 `STG/LDG.E.STRONG.SYS` + `MEMBAR.*.SYS` = the st.release.sys / ld.acquire.sys flag protocol of the cross-GPU barrier
-(the data loads/stores on peer-mapped pointers are ordinary `LDG`/`STG`: the address aperture routes them over NVLink).
+(the data loads/stores on peer-mapped pointers are ordinary `LDG`/`STG`: the address aperture routes them over NVLink);
+`LDGMC.E.ADD.F32x4...SYS` = multimem.ld_reduce (NVSwitch in-fabric reduction), the matching multimem.st shows as a `.SYS` store.
 """
 
 
@@ -35,7 +38,7 @@ def main():
         cnt = collections.Counter(m.group(1) for m in map(MN.match, lines) if m)
         md.append(f"\n## `{name}`\n\ntotal SASS instructions: {sum(cnt.values())}\n\n| mnemonic | count |\n|---|---|")
         md += [f"| {k} | {cnt[k]} |" for k in sorted((k for k in cnt if KEEP.match(k)), key=lambda k: -cnt[k])]
-        pick = [i for i, l in enumerate(lines) if "UTCHMMA" in l or "UTMALDG" in l or ".SYS" in l]
+        pick = [i for i, l in enumerate(lines) if "UTCHMMA" in l or "UTMALDG" in l or "LDGMC" in l or ".SYS" in l]
         if pick:
             lo = max(0, pick[0] - 12)
             ex = [l[:130].rstrip() for l in lines[lo:lo + 70] if re.search(r"/\*[0-9a-f]{4,5}\*/\s+\S", l)]
