@@ -79,11 +79,13 @@ struct FwdShape {
     int NT;          // output channels per CTA (16 .. 128)
     int R;           // rows per activation tile = 128 + K - 1
     int MT;          // 128-position tiles per CTA (1, 2 or 4): weights are streamed once for all of them
+    int slot;        // 0: a tile is 128 positions of one sample.  > 0 (16/32/64): short windows (L + K - 1 <= slot):
+                     // a tile packs 128/slot SAMPLES, each in its own `slot` rows (windows never straddle slots)
 };
 
 __global__ void __launch_bounds__(kFwdThreads, 1)
 conv1d_fwd_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_w,
-                  const float* __restrict__ bias, __nv_bfloat16* __restrict__ y, FwdShape s) {
+                  const __grid_constant__ CUtensorMap map_xs, const float* __restrict__ bias, __nv_bfloat16* __restrict__ y, FwdShape s) {
     extern __shared__ __align__(128) uint8_t smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int n0 = blockIdx.x * s.NT, l0 = blockIdx.y * 128 * s.MT, b = blockIdx.z;
@@ -107,13 +109,14 @@ conv1d_fwd_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
         for (int i = 0; i < kWStages; ++i) { mbar_init(full_w + i, 1); mbar_init(empty_w + i, 1); }
         mbar_init(acc_full, 1);
         fence_mbar_init();
-        tma_prefetch_desc(&map_x); tma_prefetch_desc(&map_w);
+        tma_prefetch_desc(&map_x); tma_prefetch_desc(&map_w); tma_prefetch_desc(&map_xs);
     }
     if (warp == 1) tmem_alloc(tmem_slot, tmem_cols);
     tc_fence_before_sync();
     __syncthreads();
     tc_fence_after_sync();
     const uint32_t tmem_base = *tmem_slot;
+    const int spt = s.slot ? 128 / s.slot : 1;              // samples per tile in packed mode
 
     if (warp == 0) {
         // ===== TMA producer =====
@@ -122,10 +125,22 @@ conv1d_fwd_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
             for (int c = 0; c < chunks; ++c) {
                 const int sa = c % kAStages;
                 if (c >= kAStages) mbar_wait(empty_a + sa, ((c / kAStages) - 1) & 1);
-                mbar_arrive_expect_tx(full_a + sa, a_tile * s.MT);
-                for (int i = 0; i < s.MT; ++i)
-                    tma_load_4d(a_ring + sa * a_stride + i * a_tile_stride, &map_x, full_a + sa, 0, l0 + i * 128 - s.pad,
-                                c * (s.CK / 8), b);
+                if (!s.slot) {
+                    mbar_arrive_expect_tx(full_a + sa, a_tile * s.MT);
+                    for (int i = 0; i < s.MT; ++i)
+                        tma_load_4d(a_ring + sa * a_stride + i * a_tile_stride, &map_x, full_a + sa, 0, l0 + i * 128 - s.pad,
+                                    c * (s.CK / 8), b);
+                } else {
+                    // packed short windows: one (slot rows x 1 plane) box per (sample, plane), dropped at its slot inside the
+                    // plane-major tile; samples past the batch are fetched out of bounds (zero fill)
+                    const int planes = s.CK / 8;
+                    mbar_arrive_expect_tx(full_a + sa, s.MT * 128 * 16 * planes);
+                    for (int i = 0; i < s.MT; ++i)
+                        for (int j = 0; j < spt; ++j)
+                            for (int p = 0; p < planes; ++p)
+                                tma_load_4d(a_ring + sa * a_stride + i * a_tile_stride + p * s.R * 16 + j * s.slot * 16, &map_xs,
+                                            full_a + sa, 0, -s.pad, c * planes + p, (b * s.MT + i) * spt + j);
+                }
                 for (int k = 0; k < s.K; ++k, ++wi) {
                     const int sw = wi % kWStages;
                     if (wi >= kWStages) mbar_wait(empty_w + sw, ((wi / kWStages) - 1) & 1);
@@ -171,8 +186,10 @@ conv1d_fwd_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
         mbar_wait(acc_full, 0);
         tc_fence_after_sync();
         for (int i = 0; i < s.MT; ++i) {
-        const int l = l0 + i * 128 + q * 32 + lane;
-        __nv_bfloat16* dst = y + ((size_t)b * s.Lout + l) * s.Cout + n0;
+        const int r = q * 32 + lane;                       // accumulator row = TMEM lane
+        int l = l0 + i * 128 + r, bb = b;
+        if (s.slot) { l = r % s.slot; bb = (b * s.MT + i) * spt + r / s.slot; if (bb >= s.B) l = s.Lout; }
+        __nv_bfloat16* dst = y + ((size_t)bb * s.Lout + l) * s.Cout + n0;
         for (int c0 = 0; c0 < s.NT; c0 += 16) {
             uint32_t v[16];
             tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + i * s.NT + c0, v);
@@ -220,6 +237,15 @@ int conv1d_fwd(const void* x, const void* w, const float* bias, void* y, int B, 
     if (rc) return rc;
     const int tiles = (s.Lout + 127) / 128;
     s.MT = tiles >= 4 ? 4 : tiles;                          // TMEM: MT * NT <= 512 columns
+    // short windows: pack several samples into one 128-row tile (each in its own power-of-two slot)
+    s.slot = 0;
+    const int need = s.Lout + K - 1;                        // input rows (incl. padding) one sample's outputs read
+    if (need <= 64) {
+        s.slot = need <= 16 ? 16 : (need <= 32 ? 32 : 64);
+        s.R = (128 + K - 1 + 7) & ~7;                       // per-plane TMA destinations must stay 128-byte aligned
+        const int spt = 128 / s.slot, groups = (B + spt - 1) / spt;
+        s.MT = groups >= 4 ? 4 : groups;
+    }
     const int a_tile = (s.R * 16 * (s.CK / 8) + 127) & ~127, w_bytes = s.NT * 16 * (s.CK / 8);
     size_t smem = 256 + (size_t)kAStages * a_tile * s.MT + (size_t)kWStages * ((w_bytes + 127) & ~127);
     while (smem > 220 * 1024 && s.MT > 1) {                 // very wide taps: fewer tiles per CTA
@@ -233,8 +259,15 @@ int conv1d_fwd(const void* x, const void* w, const float* bias, void* y, int B, 
         CS_CUDA_OK(cudaFuncSetAttribute(conv1d_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured[dev & 63] = smem;
     }
+    CUtensorMap mxs = mx;
     dim3 grid(Cout / s.NT, (tiles + s.MT - 1) / s.MT, B);
-    conv1d_fwd_kernel<<<grid, kFwdThreads, smem, st>>>(mx, mw, bias, (__nv_bfloat16*)y, s);
+    if (s.slot) {
+        rc = make_plane_map(&mxs, x, B, L, Cin, s.slot, 1);
+        if (rc) return rc;
+        const int per_cta = s.MT * (128 / s.slot);
+        grid = dim3(Cout / s.NT, 1, (B + per_cta - 1) / per_cta);
+    }
+    conv1d_fwd_kernel<<<grid, kFwdThreads, smem, st>>>(mx, mw, mxs, bias, (__nv_bfloat16*)y, s);
     CS_CUDA_OK(cudaGetLastError());
     return CS_OK;
 }
