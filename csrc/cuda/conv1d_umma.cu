@@ -307,10 +307,11 @@ constexpr int kWgStages = 2;
 constexpr int kWgTapsPerPass = 7;
 constexpr int kWgNT = 64, kWgMT = 128;
 
-struct WgShape { int B, L, Lout, Cin, Cout, K, pad, k0, ktaps, R, tiles_per_sample, total_tiles, my_cout, my_cin; };
+struct WgShape { int B, L, Lout, Cin, Cout, K, pad, k0, ktaps, R, tiles_per_sample, total_tiles, my_cout, my_cin, slot; };
 
 __global__ void __launch_bounds__(kWgThreads, 1)
 conv1d_wgrad_kernel(const __grid_constant__ CUtensorMap map_dy, const __grid_constant__ CUtensorMap map_x,
+                    const __grid_constant__ CUtensorMap map_dys, const __grid_constant__ CUtensorMap map_xs,
                     float* __restrict__ dw, float* __restrict__ dbias, WgShape s) {
     extern __shared__ __align__(128) uint8_t smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -352,9 +353,23 @@ conv1d_wgrad_kernel(const __grid_constant__ CUtensorMap map_dy, const __grid_con
                 const int tile = t_begin + it, b = tile / s.tiles_per_sample, l0 = (tile % s.tiles_per_sample) * 128;
                 const int sg = it % kWgStages;
                 if (it >= kWgStages) mbar_wait(empty + sg, ((it / kWgStages) - 1) & 1);
-                mbar_arrive_expect_tx(full + sg, dy_bytes + x_bytes);
-                tma_load_4d(ring + sg * stage_bytes, &map_dy, full + sg, 0, l0, co0 / 8, b);
-                tma_load_4d(ring + sg * stage_bytes + dy_alloc, &map_x, full + sg, 0, l0 + s.k0 - s.pad, ci0 / 8, b);
+                if (!s.slot) {
+                    mbar_arrive_expect_tx(full + sg, dy_bytes + x_bytes);
+                    tma_load_4d(ring + sg * stage_bytes, &map_dy, full + sg, 0, l0, co0 / 8, b);
+                    tma_load_4d(ring + sg * stage_bytes + dy_alloc, &map_x, full + sg, 0, l0 + s.k0 - s.pad, ci0 / 8, b);
+                } else {
+                    // packed short windows: `tile` is a group of 128/slot samples, each dropped into its own slot of rows
+                    const int spt = 128 / s.slot;
+                    mbar_arrive_expect_tx(full + sg, 128 * 16 * (planes_dy + planes_x));
+                    for (int j = 0; j < spt; ++j) {
+                        for (int p = 0; p < planes_dy; ++p)
+                            tma_load_4d(ring + sg * stage_bytes + p * 128 * 16 + j * s.slot * 16, &map_dys, full + sg, 0, 0,
+                                        co0 / 8 + p, tile * spt + j);
+                        for (int p = 0; p < planes_x; ++p)
+                            tma_load_4d(ring + sg * stage_bytes + dy_alloc + p * s.R * 16 + j * s.slot * 16, &map_xs, full + sg, 0,
+                                        s.k0 - s.pad, ci0 / 8 + p, tile * spt + j);
+                    }
+                }
             }
         }
     } else if (warp == 1) {
@@ -430,9 +445,18 @@ int conv1d_wgrad(const void* x, const void* dy, float* dw, float* dbias, int B, 
     int splits = (2 * num_sms()) / (gx * gy); if (splits < 1) splits = 1; if (splits > s.total_tiles) splits = s.total_tiles;
     int dev = 0;
     CS_CUDA_OK(cudaGetDevice(&dev));
+    // short windows: pack 128/slot samples per 128-row reduction tile (every tap of a sample stays inside its slot)
+    s.slot = 0;
+    if (Lout + K - 1 <= 64) {
+        const int need = Lout + K - 1;
+        s.slot = need <= 16 ? 16 : (need <= 32 ? 32 : 64);
+        s.tiles_per_sample = 1;
+        s.total_tiles = (B + 128 / s.slot - 1) / (128 / s.slot);
+        if (splits > s.total_tiles) splits = s.total_tiles;
+    }
     for (int k0 = 0; k0 < K; k0 += kWgTapsPerPass) {
         s.k0 = k0; s.ktaps = K - k0 < kWgTapsPerPass ? K - k0 : kWgTapsPerPass;
-        s.R = 128 + s.ktaps - 1;
+        s.R = s.slot ? ((128 + s.ktaps - 1 + 7) & ~7) : 128 + s.ktaps - 1;
         CUtensorMap mdy, mx;
         int rc = make_plane_map(&mdy, dy, B, Lout, Cout, 128, s.my_cout / 8);
         if (rc) return rc;
@@ -445,7 +469,14 @@ int conv1d_wgrad(const void* x, const void* dy, float* dw, float* dbias, int B, 
             CS_CUDA_OK(cudaFuncSetAttribute(conv1d_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
             configured[dev & 63] = smem;
         }
-        conv1d_wgrad_kernel<<<dim3(gx, gy, splits), kWgThreads, smem, st>>>(mdy, mx, dw, dbias, s);
+        CUtensorMap mdys = mdy, mxs = mx;
+        if (s.slot) {
+            rc = make_plane_map(&mdys, dy, B, Lout, Cout, s.slot, 1);
+            if (rc) return rc;
+            rc = make_plane_map(&mxs, x, B, L, Cin, s.slot, 1);
+            if (rc) return rc;
+        }
+        conv1d_wgrad_kernel<<<dim3(gx, gy, splits), kWgThreads, smem, st>>>(mdy, mx, mdys, mxs, dw, dbias, s);
         CS_CUDA_OK(cudaGetLastError());
     }
     if (dbias) {
