@@ -132,21 +132,26 @@ def run_ours(args):
         dt = torch.bfloat16 if args.amp == "bf16" else torch.float32
         store = PinnedShardStore(paths, max_windows=args.num_windows, dtype=dt)
         runner.enable_e2e(store, seed=rank)
-        for _ in range(W):
-            runner.run_round_e2e()
+        for _ in range(max(W, 4)):                           # 2 eager rounds + 2 graph captures (one per staging slot)
+            runner.run_round_e2e(pipelined=True)
+        runner.drain_e2e()
         sync_all()
         t0 = time.perf_counter()
         e0.record()
         last = 0.0
         for _ in range(K):
-            last = runner.run_round_e2e()
+            last = runner.run_round_e2e(pipelined=True)      # reads the previous round's loss while this one runs
+        last = runner.drain_e2e()                            # ... and the last round's loss, still inside the timed region
         e1.record()
         sync_all()
         wall_ms = (time.perf_counter() - t0) * 1e3
-        e2e_ms = max_over_ranks(max(e0.elapsed_time(e1), wall_ms), device)
+        e2e_dev_ms = e0.elapsed_time(e1)
+        e2e_ms = max_over_ranks(max(e2e_dev_ms, wall_ms), device)
         e2e = {"value": samples / (e2e_ms / 1e3), "unit": "samples/s",
                "h2d_bytes_per_step": int(runner._stager.h2d_bytes), "d2h_bytes_per_step": int(runner.d2h_bytes),
-               "ms_per_step": e2e_ms / K, "stage_dtype": str(dt).replace("torch.", ""), "last_loss": last}
+               "ms_per_step": e2e_ms / K, "device_ms_per_step": e2e_dev_ms / K, "wall_ms_per_step": wall_ms / K, "stage_dtype": str(dt).replace("torch.", ""), "last_loss": last,
+               "loss_readback": "every round's loss is copied device->host and read by the host, pipelined one round "
+                                "behind the enqueue (drained inside the timed region)"}
     clocks = sampler.stop()
     status = runner.agg.comm.status() if getattr(runner.agg, "comm", None) is not None else 0
 

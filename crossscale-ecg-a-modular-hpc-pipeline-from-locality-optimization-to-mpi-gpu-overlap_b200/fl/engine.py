@@ -439,7 +439,9 @@ class FedAvgRunner:
         self._store, self._sampler = store, BlockSampler(store.n, rows, seed)
         self._stager = H2DStager(rows, store.l, store.x.dtype, self.device)
         self._loss_host = torch.zeros(8, dtype=torch.float32, pin_memory=True)
-        self._loss_prev = 0.0
+        self._loss_prev, self._last_loss, self._e2e_rounds = 0.0, 0.0, 0
+        self._loss_events = [torch.cuda.Event(), torch.cuda.Event()]
+        self._loss_seen = [None, None]
         self._graphs = [None, None]
         self._slot = 0
         self._lib = _lib
@@ -450,8 +452,13 @@ class FedAvgRunner:
         hx, hy = self._store.block(self._sampler.next_start(), self.local_steps * self.batch)
         self._stager.stage(slot, hx, hy)
 
-    def run_round_e2e(self) -> float:
-        """One FL round fed from pinned host memory; returns the round's mean loss (host float)."""
+    def run_round_e2e(self, pipelined: bool = False) -> float:
+        """One FL round fed from pinned host memory; returns a round's mean loss (host float).
+
+        ``pipelined=False``: the host waits for THIS round's loss before returning.
+        ``pipelined=True``: this round is enqueued (H2D of the next block, 50 fused steps, aggregation, D2H of the
+        loss) and the host then collects the PREVIOUS round's loss, so the next round can be enqueued while this one
+        runs; every round's loss is still read back, one round late — call :meth:`drain_e2e` for the last one."""
         slot = self._slot
         xb, yb = self._stager.acquire(slot)
         self._stage_next(slot ^ 1)                  # next block's H2D overlaps this round's compute
@@ -474,14 +481,29 @@ class FedAvgRunner:
         self._stager.release(slot)
         self.agg.aggregate(self.flat, self.prev, self.weight, self.mom)
         st = torch.cuda.current_stream(self.device)
-        self._lib.check(self._lib.cuda_lib().cs_stage_d2h(self._loss_host.data_ptr(), tr.state.fstate.data_ptr(),
+        k = self._e2e_rounds & 1                       # two pinned loss slots / events: one in flight, one being read
+        self._lib.check(self._lib.cuda_lib().cs_stage_d2h(self._loss_host.data_ptr() + 16 * k, tr.state.fstate.data_ptr(),
                                                           4, st.cuda_stream), "cs_stage_d2h")
-        st.synchronize()
-        total = float(self._loss_host[0])
-        loss = (total - self._loss_prev) / self.local_steps
-        self._loss_prev = total
+        self._loss_events[k].record(st)
+        self._e2e_rounds += 1
         self._slot ^= 1
-        return loss
+        if pipelined and self._e2e_rounds > 1:
+            return self._collect_loss(k ^ 1)           # previous round (already or almost done)
+        return self._collect_loss(k)
+
+    def _collect_loss(self, k: int) -> float:
+        self._loss_events[k].synchronize()
+        total = float(self._loss_host[4 * k])
+        if total == self._loss_seen[k]:                # this slot was already consumed
+            return self._last_loss
+        self._loss_seen[k] = total
+        self._last_loss = (total - self._loss_prev) / self.local_steps
+        self._loss_prev = total
+        return self._last_loss
+
+    def drain_e2e(self) -> float:
+        """Read the loss of the last enqueued round (pipelined mode)."""
+        return self._collect_loss((self._e2e_rounds - 1) & 1)
 
     def close(self):
         if getattr(self.agg, "inplace", False):          # parameters live in the arena: move them out before it is freed
