@@ -283,19 +283,20 @@ def _run_pseudo(model, batch_iter, device, steps, rank, batch_size, world, amp, 
     fused = (device.type == "cuda" and isinstance(model, TinyECG) and tk.use_kernels()
              and x_gpu is not None and model.num_classes <= tk.MAX_CLASSES)
     if fused:
+        # the steps run as replays of one CUDA graph of `chunk` fused steps (steps is rounded up to whole chunks)
         chunk = min(steps, 50)
         tr = FusedTinyTrainer(model, x_gpu, y_gpu, batch_size, chunk, amp=amp)
-        tr.run_round_resident()                       # warm-up + graph capture, not timed
+        tr.run_round_resident()                       # eager warm-up
+        tr.run_round_resident()                       # graph capture + first replay
         torch.cuda.synchronize()
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        done, a_rec = 0, False
+        a.record()
+        done = 0
         while done < steps:
-            if not a_rec:
-                a.record(); a_rec = True
             tr.run_round_resident()
             done += chunk
-            if rank == 0 and done % 10 == 0:
-                pass
+            if rank == 0:
+                print(f"[{label}] step {done}/{steps}", flush=True)
         b.record()
         torch.cuda.synchronize()
         return _bench_row(label, world, rank, batch_size, done, 0.0, 0.0, a.elapsed_time(b))
