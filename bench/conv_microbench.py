@@ -91,8 +91,11 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--quick", action="store_true")
     ap.add_argument("--out", default="results/conv_microbench.csv")
+    ap.add_argument("--cases", default="", help='explicit "B,C,K;B,C,K;..." list (L = 500)')
     a = ap.parse_args()
-    if a.quick:
+    if a.cases:
+        grid = [(int(b), 500, int(c), int(k)) for b, c, k in (t.split(",") for t in a.cases.split(";"))]
+    elif a.quick:
         grid = [(256, 500, 16, 5), (256, 500, 64, 7), (256, 500, 256, 7), (1024, 500, 128, 3), (64, 500, 256, 31)]
     else:
         grid = [(B, 500, C, K) for B in (32, 256, 1024, 4096) for C in (16, 64, 256) for K in (3, 7, 31)

@@ -18,6 +18,7 @@
 #include "common/tcgen05.cuh"
 
 #include <cuda.h>
+#include <stdlib.h>
 #include <string.h>
 
 namespace cs {
@@ -216,6 +217,8 @@ conv1d_fwd_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
     if (warp == 1) tmem_dealloc(tmem_base, tmem_cols);
 }
 
+static int conv1d_fwd_sw128(const void* x, const void* w, const float* bias, void* y, int B, int L, int Cin, int Cout, int K,
+                            int pad, int relu, int Lout, cudaStream_t st);
 static int pick_ck(int C) { return C % 64 == 0 ? 64 : (C % 32 == 0 ? 32 : 16); }
 static int pick_nt(int C) { return C % 128 == 0 ? 128 : (C % 64 == 0 ? 64 : (C % 32 == 0 ? 32 : 16)); }
 
@@ -229,6 +232,10 @@ int conv1d_fwd(const void* x, const void* w, const float* bias, void* y, int B, 
     s.B = B; s.L = L; s.Cin = Cin; s.Cout = Cout; s.K = K; s.pad = pad; s.relu = relu;
     s.Lout = L + 2 * pad - K + 1;
     CS_REQUIRE(s.Lout >= 1, "conv1d: empty output");
+    {
+        const int rc128 = conv1d_fwd_sw128(x, w, bias, y, B, L, Cin, Cout, K, pad, relu, s.Lout, st);
+        if (rc128 >= 0) return rc128;
+    }
     s.CK = pick_ck(Cin); s.NT = pick_nt(Cout); s.R = 128 + K - 1;
     CUtensorMap mx, mw;
     int rc = make_plane_map(&mx, x, B, L, Cin, s.R, s.CK / 8);
@@ -268,6 +275,280 @@ int conv1d_fwd(const void* x, const void* w, const float* bias, void* y, int B, 
         grid = dim3(Cout / s.NT, 1, (B + per_cta - 1) / per_cta);
     }
     conv1d_fwd_kernel<<<grid, kFwdThreads, smem, st>>>(mx, mw, mxs, bias, (__nv_bfloat16*)y, s);
+    CS_CUDA_OK(cudaGetLastError());
+    return CS_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// K1, wide-channel variant (Cin % 64 == 0, L long enough for 128-position tiles).
+// The plane layout above costs one TMA "row" per 16 bytes: at C = 256 the copy engine, not the tensor core,
+// sets the pace (ncu: tensor pipe 46 % active, L2 sectors 1.7x the useful bytes).  Here both operands are
+// staged as 128-byte rows (64 channels) with the 128-byte swizzle, 8x fewer TMA rows for the same bytes:
+//   A tile  = R rows (positions) x 128 B, K-major SWIZZLE_128B;  W tile = NT rows (cout) x 128 B.
+// A tap is still a start-address shift (tap * 128 B).  That start is not aligned to the 1024-byte swizzle
+// pattern, and that is fine: the tensor core applies the XOR to the ABSOLUTE shared-memory address bits
+// (the same ones TMA used when it wrote the tile), so row r+tap is found where TMA put it.  Measured on
+// B200: with the descriptor's base-offset field left 0 the results match the fp32 oracle; setting it to
+// (start >> 7) & 7 double-counts the phase and gives wrong sums.
+// The epilogue packs bf16 rows into a swizzled 32-row slab per warp and writes it with one TMA store
+// (128-byte rows; rows past Lout are clipped by the tensor map) instead of 16-byte scattered stores.
+// ------------------------------------------------------------------------------------------------
+struct Fwd128Shape {
+    int B, L, Lout, Cin, Cout, K, pad, relu;
+    int NT, R;               // cout per CTA, rows per A tile (128 + K - 1)
+    int MT;                  // 128-position tiles per CTA (each with its own TMEM accumulator); the tiles of a CTA are
+                             // consecutive entries of the flat (sample, tile) list, so a CTA may straddle two samples
+    int AS, WS;              // activation ring stages (1 or 2), weight ring stages (2..8)
+    int tiles, total;        // tiles per sample, B * tiles
+    int tile_stride;         // bytes between the MT A tiles of one stage (multiple of 1024)
+    int tma_store;           // epilogue through shared memory + TMA store (NT % 64 == 0)
+};
+
+constexpr int kMaxWStages = 8;
+
+static int make_row_map(CUtensorMap* m, const void* base, int outer, int rows, int C, int box_rows) {
+    // [outer, rows, C] bf16 viewed as (C, rows, outer); box = 64 channels (one 128-byte swizzled row) x box_rows
+    EncodeTiledFn fn = encode_fn();
+    CS_REQUIRE(fn != nullptr, "cuTensorMapEncodeTiled not available from this driver");
+    cuuint64_t dims[3] = {(cuuint64_t)C, (cuuint64_t)rows, (cuuint64_t)outer};
+    cuuint64_t strides[2] = {(cuuint64_t)C * 2, (cuuint64_t)rows * C * 2};
+    cuuint32_t box[3] = {64, (cuuint32_t)box_rows, 1};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    CS_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled (128B rows) failed (%d) rows=%d C=%d box_rows=%d", (int)r, rows, C, box_rows);
+    return CS_OK;
+}
+
+// Sized so that TWO CTAs fit one SM (<= 113 KB shared, <= 256 TMEM columns each): while one CTA drains its
+// accumulators and ramps up its first loads the other keeps the tensor core busy (measured 1.16 -> 1.36
+// PFLOP/s at C = 256, K = 7 against one 4-tile CTA per SM).
+__global__ void __launch_bounds__(kFwdThreads, 1)
+conv1d_fwd_sw128_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_w,
+                        const __grid_constant__ CUtensorMap map_y, const float* __restrict__ bias, __nv_bfloat16* __restrict__ y,
+                        Fwd128Shape s) {
+    extern __shared__ uint8_t smem_raw[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int n0 = blockIdx.x * s.NT, t0 = (blockIdx.z * gridDim.y + blockIdx.y) * s.MT;
+    if (t0 >= s.total) return;                               // padding CTAs of the (y, z) split
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw);
+    uint64_t* full_a = bars, *empty_a = bars + 2, *full_w = bars + 4, *empty_w = full_w + kMaxWStages;
+    uint64_t* acc_full = empty_w + kMaxWStages;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_full + 1);
+    // operand rings start on a 1024-byte boundary of the shared window (the swizzle pattern is address based)
+    uint8_t* a_ring = smem_raw + (((smem_u32(smem_raw) + 256 + 1023) & ~1023u) - smem_u32(smem_raw));
+    const int a_bytes = s.tile_stride * s.MT;
+    const int w_bytes = s.NT * 128;
+    uint8_t* w_ring = a_ring + s.AS * a_bytes;
+    const int chunks = s.Cin / 64;
+    uint32_t tmem_cols = 32;
+    while ((int)tmem_cols < s.NT * s.MT) tmem_cols <<= 1;
+
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < s.AS; ++i) { mbar_init(full_a + i, 1); mbar_init(empty_a + i, 1); }
+        for (int i = 0; i < s.WS; ++i) { mbar_init(full_w + i, 1); mbar_init(empty_w + i, 1); }
+        mbar_init(acc_full, 1);
+        fence_mbar_init();
+        tma_prefetch_desc(&map_x); tma_prefetch_desc(&map_w); tma_prefetch_desc(&map_y);
+    }
+    if (warp == 1) tmem_alloc(tmem_slot, tmem_cols);
+    tc_fence_before_sync();
+    __syncthreads();
+    tc_fence_after_sync();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===== TMA producer =====
+        if (elect_one()) {
+            int wi = 0;
+            for (int c = 0; c < chunks; ++c) {
+                const int sa = c % s.AS;
+                if (c >= s.AS) mbar_wait(empty_a + sa, ((c / s.AS) - 1) & 1);
+                mbar_arrive_expect_tx(full_a + sa, s.R * 128 * s.MT);
+                for (int i = 0; i < s.MT; ++i) {
+                    // tiles past the end of the list are fetched out of bounds (sample index >= B): zero fill
+                    const int t = t0 + i, tb = t / s.tiles, tl = (t % s.tiles) * 128;
+                    tma_load_3d(a_ring + sa * a_bytes + i * s.tile_stride, &map_x, full_a + sa, c * 64, tl - s.pad, tb);
+                }
+                for (int k = 0; k < s.K; ++k, ++wi) {
+                    const int sw = wi % s.WS;
+                    if (wi >= s.WS) mbar_wait(empty_w + sw, ((wi / s.WS) - 1) & 1);
+                    mbar_arrive_expect_tx(full_w + sw, w_bytes);
+                    tma_load_3d(w_ring + sw * w_bytes, &map_w, full_w + sw, c * 64, n0, k);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer =====
+        if (elect_one()) {
+            const uint32_t idesc = idesc_f16(FMT_BF16, 128, s.NT, MAJOR_K, MAJOR_K);
+            int wi = 0;
+            uint32_t first = 1;
+            for (int c = 0; c < chunks; ++c) {
+                const int sa = c % s.AS;
+                mbar_wait(full_a + sa, (c / s.AS) & 1);
+                tc_fence_after_sync();
+                const uint32_t a_addr = smem_u32(a_ring + sa * a_bytes);
+                for (int k = 0; k < s.K; ++k, ++wi) {
+                    const int sw = wi % s.WS;
+                    mbar_wait(full_w + sw, (wi / s.WS) & 1);
+                    tc_fence_after_sync();
+                    const uint64_t b0 = smem_desc_sw128(smem_u32(w_ring + sw * w_bytes), 1024);
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {            // 4 x 16 channels inside the 128-byte row
+                        for (int i = 0; i < s.MT; ++i) {
+                            // tap k = k rows (k * 128 B) further down the tile; 16-channel step = 32 B inside the row
+                            const uint64_t a = smem_desc_sw128(a_addr + i * s.tile_stride + k * 128 + j * 32, 1024);
+                            mma_f16(tmem_base + i * s.NT, a, b0 + (uint64_t)(j * 2), idesc, (first && j == 0) ? 0u : 1u);
+                        }
+                    }
+                    first = 0;
+                    mma_commit(empty_w + sw);
+                }
+                mma_commit(empty_a + sa);
+            }
+            mma_commit(acc_full);
+        }
+    } else {
+        // ===== epilogue: TMEM -> registers -> bias/ReLU -> bf16 -> (swizzled slab -> TMA store | global) =====
+        const int q = warp & 3;
+        mbar_wait(acc_full, 0);                              // every MMA retired: the operand rings are free
+        tc_fence_after_sync();
+        if (s.tma_store) {
+            // two 4 KB slabs per warp inside the (now idle) activation ring; slab row r = accumulator lane
+            uint8_t* slabs = a_ring + q * 8192;
+            int n_store = 0;
+            for (int i = 0; i < s.MT; ++i) {
+                const int t = t0 + i, tb = t / s.tiles, tl = (t % s.tiles) * 128 + q * 32;
+                if (t >= s.total || tl >= s.Lout) continue;
+                for (int hh = 0; hh < s.NT; hh += 64, ++n_store) {
+                    uint8_t* slab = slabs + (n_store & 1) * 4096;
+                    uint32_t v[64];
+                    const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + i * s.NT + hh;
+                    tmem_ld32(taddr, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
+                    tmem_ld32(taddr + 32, *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
+                    if (n_store >= 2) {                       // the store that last read this slab must be done with it
+                        if (lane == 0) tma_store_wait_read<1>();
+                        __syncwarp();
+                    }
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int c = 0; c < 8; ++c) {
+                        uint32_t pk[4];
+#pragma unroll
+                        for (int j = 0; j < 8; j += 2) {
+                            float f0 = __uint_as_float(v[c * 8 + j]), f1 = __uint_as_float(v[c * 8 + j + 1]);
+                            if (bias) { f0 += __ldg(bias + n0 + hh + c * 8 + j); f1 += __ldg(bias + n0 + hh + c * 8 + j + 1); }
+                            if (s.relu) { f0 = fmaxf(f0, 0.0f); f1 = fmaxf(f1, 0.0f); }
+                            __nv_bfloat162 h2 = __floats2bfloat162_rn(f0, f1);
+                            pk[j >> 1] = *reinterpret_cast<uint32_t*>(&h2);
+                        }
+                        *reinterpret_cast<uint4*>(slab + lane * 128 + ((c ^ (lane & 7)) << 4)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                    }
+                    fence_proxy_async_smem();
+                    __syncwarp();
+                    if (lane == 0) {
+                        tma_store_3d(&map_y, slab, n0 + hh, tl, tb);     // rows past Lout are clipped by the map
+                        tma_store_commit();
+                    }
+                }
+            }
+            if (lane == 0) tma_store_wait_read<0>();
+            __syncwarp();
+        } else {
+            for (int i = 0; i < s.MT; ++i) {
+                const int t = t0 + i, tb = t / s.tiles, l = (t % s.tiles) * 128 + q * 32 + lane;
+                if (t >= s.total) continue;
+                __nv_bfloat16* dst = y + ((size_t)tb * s.Lout + l) * s.Cout + n0;
+                for (int c0 = 0; c0 < s.NT; c0 += 32) {
+                    uint32_t v[32];
+                    tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + i * s.NT + c0, v);
+                    tmem_ld_wait();
+                    if (l < s.Lout) {
+#pragma unroll
+                        for (int h = 0; h < 32; h += 8) {
+                            uint32_t pk[4];
+#pragma unroll
+                            for (int j = 0; j < 8; j += 2) {
+                                float f0 = __uint_as_float(v[h + j]), f1 = __uint_as_float(v[h + j + 1]);
+                                if (bias) { f0 += bias[n0 + c0 + h + j]; f1 += bias[n0 + c0 + h + j + 1]; }
+                                if (s.relu) { f0 = fmaxf(f0, 0.0f); f1 = fmaxf(f1, 0.0f); }
+                                __nv_bfloat162 hh = __floats2bfloat162_rn(f0, f1);
+                                pk[j >> 1] = *reinterpret_cast<uint32_t*>(&hh);
+                            }
+                            *reinterpret_cast<uint4*>(dst + c0 + h) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                        }
+                    }
+                }
+            }
+        }
+    }
+    tc_fence_before_sync();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc(tmem_base, tmem_cols);
+}
+
+static int env_int(const char* name, int dflt) {
+    const char* e = getenv(name);
+    return (e && *e) ? atoi(e) : dflt;
+}
+
+// Launches the 128-byte-row variant and returns CS_OK (or an error), or -1 when the shape is not one it covers.
+// Tuning overrides for experiments: CS_CONV_SW128=0 (use the plane kernel), CS_CONV_MT / CS_CONV_AS / CS_CONV_WS.
+static int conv1d_fwd_sw128(const void* x, const void* w, const float* bias, void* y, int B, int L, int Cin, int Cout, int K,
+                            int pad, int relu, int Lout, cudaStream_t st) {
+    if (Cin % 64 != 0 || Cout % 32 != 0 || Lout + K - 1 <= 64 || !env_int("CS_CONV_SW128", 1)) return -1;
+    Fwd128Shape s;
+    s.B = B; s.L = L; s.Lout = Lout; s.Cin = Cin; s.Cout = Cout; s.K = K; s.pad = pad; s.relu = relu;
+    s.NT = Cout % 128 == 0 ? 128 : (Cout % 64 == 0 ? 64 : 32);
+    s.R = 128 + K - 1;
+    s.tile_stride = (s.R * 128 + 1023) & ~1023;
+    s.tiles = (Lout + 127) / 128;
+    s.total = B * s.tiles;
+    auto need = [&]() { return (size_t)2048 + (size_t)s.AS * s.tile_stride * s.MT + (size_t)s.WS * s.NT * 128; };
+    // preferred: two co-resident CTAs per SM (256 TMEM columns and <= 113 KB shared memory each)
+    const size_t kHalfSm = 113 * 1024, kFullSm = 227 * 1024;
+    s.MT = 256 / s.NT; if (s.MT > 4) s.MT = 4; if (s.MT > s.total) s.MT = s.total;
+    s.AS = 2; s.WS = 4;
+    while (need() > kHalfSm && s.WS > 2) --s.WS;
+    if (need() > kHalfSm) {                                  // wide taps: one activation stage, the sibling CTA covers the bubble
+        s.AS = 1; s.WS = 4;
+        while (need() > kHalfSm && s.WS > 2) --s.WS;
+    }
+    if (need() > kHalfSm) {                                  // very wide taps: one CTA per SM, all of TMEM
+        s.AS = 2; s.WS = 4;
+        s.MT = 512 / s.NT; if (s.MT > 4) s.MT = 4; if (s.MT > s.total) s.MT = s.total;
+        while (need() > kFullSm && s.MT > 1) s.MT >>= 1;
+        while (need() > kFullSm && s.WS > 2) --s.WS;
+        if (need() > kFullSm) return -1;
+    }
+    { const int v = env_int("CS_CONV_MT", 0); if (v > 0 && v * s.NT <= 512) s.MT = v; }
+    { const int v = env_int("CS_CONV_AS", 0); if (v == 1 || v == 2) s.AS = v; }
+    { const int v = env_int("CS_CONV_WS", 0); if (v >= 2 && v <= kMaxWStages) s.WS = v; }
+    if (need() > kFullSm) return -1;
+    s.tma_store = (s.NT % 64 == 0 && (size_t)s.AS * s.tile_stride * s.MT >= 32768) ? 1 : 0;
+    CUtensorMap mx, mw;
+    int rc = make_row_map(&mx, x, B, L, Cin, s.R);
+    if (rc) return rc;
+    rc = make_row_map(&mw, w, K, Cout, Cin, s.NT);
+    if (rc) return rc;
+    CUtensorMap my = mw;
+    if (s.tma_store) {
+        rc = make_row_map(&my, y, B, Lout, Cout, 32);
+        if (rc) return rc;
+    }
+    const size_t smem = need();
+    static size_t configured[64] = {};
+    int dev = 0;
+    CS_CUDA_OK(cudaGetDevice(&dev));
+    if (smem > configured[dev & 63]) {
+        CS_CUDA_OK(cudaFuncSetAttribute(conv1d_fwd_sw128_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured[dev & 63] = smem;
+    }
+    const int units = (s.total + s.MT - 1) / s.MT, gy = units < 32768 ? units : 32768;
+    dim3 grid(Cout / s.NT, gy, (units + gy - 1) / gy);
+    conv1d_fwd_sw128_kernel<<<grid, kFwdThreads, smem, st>>>(mx, mw, my, bias, (__nv_bfloat16*)y, s);
     CS_CUDA_OK(cudaGetLastError());
     return CS_OK;
 }
