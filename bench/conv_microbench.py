@@ -91,10 +91,13 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--quick", action="store_true")
     ap.add_argument("--out", default="results/conv_microbench.csv")
-    ap.add_argument("--cases", default="", help='explicit "B,C,K;B,C,K;..." list (L = 500)')
+    ap.add_argument("--cases", default="", help='explicit "B,C,K;..." (L = 500) or "B,L,C,K;..." list')
     a = ap.parse_args()
     if a.cases:
-        grid = [(int(b), 500, int(c), int(k)) for b, c, k in (t.split(",") for t in a.cases.split(";"))]
+        grid = []
+        for t in a.cases.split(";"):
+            v = [int(z) for z in t.split(",")]
+            grid.append((v[0], 500, v[1], v[2]) if len(v) == 3 else tuple(v))
     elif a.quick:
         grid = [(256, 500, 16, 5), (256, 500, 64, 7), (256, 500, 256, 7), (1024, 500, 128, 3), (64, 500, 256, 31)]
     else:
@@ -104,9 +107,9 @@ def main():
     for case in grid:
         r = bench_case(*case)
         rows.append(r)
-        print(f"B={r['B']:5d} C={r['C']:4d} K={r['K']:3d}: fwd ours {r['ours_fwd_ms']:.3f} ms ({r['ours_fwd_tflops']:.1f} TF) "
+        print(f"B={r['B']:5d} L={r['L']:4d} C={r['C']:4d} K={r['K']:3d}: fwd ours {r['ours_fwd_ms']:.3f} ms ({r['ours_fwd_tflops']:.1f} TF) "
               f"cuDNN {r['cudnn_fwd_ms']:.3f} ms ({r['cudnn_fwd_tflops']:.1f} TF) x{r['fwd_speedup']:.2f} | "
-              f"bwd ours {r['ours_dgrad_ms'] + r['ours_wgrad_ms']:.3f} cuDNN {r['cudnn_bwd_ms']:.3f} x{r['bwd_speedup']:.2f}", flush=True)
+              f"dgrad {r['ours_dgrad_ms']:.3f} wgrad {r['ours_wgrad_ms']:.3f} | bwd ours {r['ours_dgrad_ms'] + r['ours_wgrad_ms']:.3f} cuDNN {r['cudnn_bwd_ms']:.3f} x{r['bwd_speedup']:.2f}", flush=True)
     if os.path.exists(a.out):
         os.remove(a.out)
     append_results(rows, a.out)

@@ -107,6 +107,17 @@ __device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t saddr, uint32_t sbo
     return d;
 }
 
+// 128-byte swizzle, MN-major (rows = 8-deep K groups of 128 B = 64 MN elements): LBO = stride between
+// 64-element MN blocks, SBO = stride between groups of 8 K rows (1024 B when rows are packed)
+__device__ __forceinline__ uint64_t smem_desc_sw128_mn(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+    uint64_t d = (uint64_t)((saddr & 0x3FFFFu) >> 4);
+    d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFFu) << 16;
+    d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFFu) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)2 << 61;
+    return d;
+}
+
 enum : uint32_t { FMT_F16 = 0, FMT_BF16 = 1 };
 enum : uint32_t { MAJOR_K = 0, MAJOR_MN = 1 };
 // kind::f16 instruction descriptor: D=f32, A/B format, majors, N>>3 at bit 17, M>>4 at bit 24

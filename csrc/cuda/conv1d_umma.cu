@@ -18,6 +18,7 @@
 #include "common/tcgen05.cuh"
 
 #include <cuda.h>
+#include <math.h>
 #include <stdlib.h>
 #include <string.h>
 
@@ -302,6 +303,8 @@ struct Fwd128Shape {
     int tiles, total;        // tiles per sample, B * tiles
     int tile_stride;         // bytes between the MT A tiles of one stage (multiple of 1024)
     int tma_store;           // epilogue through shared memory + TMA store (NT % 64 == 0)
+    int slot;                // 0, or 32 / 64: short windows (Lout + K - 1 <= slot), a tile packs 128/slot whole samples, each
+                             // in its own `slot` rows (the taps of one sample never reach the next sample's outputs)
 };
 
 constexpr int kMaxWStages = 8;
@@ -326,8 +329,8 @@ static int make_row_map(CUtensorMap* m, const void* base, int outer, int rows, i
 // PFLOP/s at C = 256, K = 7 against one 4-tile CTA per SM).
 __global__ void __launch_bounds__(kFwdThreads, 1)
 conv1d_fwd_sw128_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_w,
-                        const __grid_constant__ CUtensorMap map_y, const float* __restrict__ bias, __nv_bfloat16* __restrict__ y,
-                        Fwd128Shape s) {
+                        const __grid_constant__ CUtensorMap map_y, const __grid_constant__ CUtensorMap map_xs,
+                        const float* __restrict__ bias, __nv_bfloat16* __restrict__ y, Fwd128Shape s) {
     extern __shared__ uint8_t smem_raw[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int n0 = blockIdx.x * s.NT, t0 = (blockIdx.z * gridDim.y + blockIdx.y) * s.MT;
@@ -350,7 +353,7 @@ conv1d_fwd_sw128_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_
         for (int i = 0; i < s.WS; ++i) { mbar_init(full_w + i, 1); mbar_init(empty_w + i, 1); }
         mbar_init(acc_full, 1);
         fence_mbar_init();
-        tma_prefetch_desc(&map_x); tma_prefetch_desc(&map_w); tma_prefetch_desc(&map_y);
+        tma_prefetch_desc(&map_x); tma_prefetch_desc(&map_w); tma_prefetch_desc(&map_y); tma_prefetch_desc(&map_xs);
     }
     if (warp == 1) tmem_alloc(tmem_slot, tmem_cols);
     tc_fence_before_sync();
@@ -365,11 +368,22 @@ conv1d_fwd_sw128_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_
             for (int c = 0; c < chunks; ++c) {
                 const int sa = c % s.AS;
                 if (c >= s.AS) mbar_wait(empty_a + sa, ((c / s.AS) - 1) & 1);
-                mbar_arrive_expect_tx(full_a + sa, s.R * 128 * s.MT);
-                for (int i = 0; i < s.MT; ++i) {
-                    // tiles past the end of the list are fetched out of bounds (sample index >= B): zero fill
-                    const int t = t0 + i, tb = t / s.tiles, tl = (t % s.tiles) * 128;
-                    tma_load_3d(a_ring + sa * a_bytes + i * s.tile_stride, &map_x, full_a + sa, c * 64, tl - s.pad, tb);
+                if (!s.slot) {
+                    mbar_arrive_expect_tx(full_a + sa, s.R * 128 * s.MT);
+                    for (int i = 0; i < s.MT; ++i) {
+                        // tiles past the end of the list are fetched out of bounds (sample index >= B): zero fill
+                        const int t = t0 + i, tb = t / s.tiles, tl = (t % s.tiles) * 128;
+                        tma_load_3d(a_ring + sa * a_bytes + i * s.tile_stride, &map_x, full_a + sa, c * 64, tl - s.pad, tb);
+                    }
+                } else {
+                    // one `slot`-row box per sample; rows 128 .. R-1 of the tile are never written and only feed outputs
+                    // that the epilogue drops (l >= Lout of the last sample)
+                    const int spt = 128 / s.slot;
+                    mbar_arrive_expect_tx(full_a + sa, 128 * 128 * s.MT);
+                    for (int i = 0; i < s.MT; ++i)
+                        for (int j = 0; j < spt; ++j)
+                            tma_load_3d(a_ring + sa * a_bytes + i * s.tile_stride + j * s.slot * 128, &map_xs, full_a + sa, c * 64,
+                                        -s.pad, (t0 + i) * spt + j);
                 }
                 for (int k = 0; k < s.K; ++k, ++wi) {
                     const int sw = wi % s.WS;
@@ -420,8 +434,10 @@ conv1d_fwd_sw128_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_
             uint8_t* slabs = a_ring + q * 8192;
             int n_store = 0;
             for (int i = 0; i < s.MT; ++i) {
-                const int t = t0 + i, tb = t / s.tiles, tl = (t % s.tiles) * 128 + q * 32;
-                if (t >= s.total || tl >= s.Lout) continue;
+                const int t = t0 + i;
+                int tb = t / s.tiles, tl = (t % s.tiles) * 128 + q * 32;
+                if (s.slot) { tb = t * (128 / s.slot) + (q * 32) / s.slot; tl = (q * 32) % s.slot; }
+                if (t >= s.total || tl >= s.Lout || tb >= s.B) continue;
                 for (int hh = 0; hh < s.NT; hh += 64, ++n_store) {
                     uint8_t* slab = slabs + (n_store & 1) * 4096;
                     uint32_t v[64];
@@ -458,8 +474,10 @@ conv1d_fwd_sw128_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_
             __syncwarp();
         } else {
             for (int i = 0; i < s.MT; ++i) {
-                const int t = t0 + i, tb = t / s.tiles, l = (t % s.tiles) * 128 + q * 32 + lane;
-                if (t >= s.total) continue;
+                const int t = t0 + i;
+                int tb = t / s.tiles, l = (t % s.tiles) * 128 + q * 32 + lane;
+                if (s.slot) { tb = t * (128 / s.slot) + (q * 32 + lane) / s.slot; l = (q * 32 + lane) % s.slot; }
+                if (t >= s.total || tb >= s.B) continue;
                 __nv_bfloat16* dst = y + ((size_t)tb * s.Lout + l) * s.Cout + n0;
                 for (int c0 = 0; c0 < s.NT; c0 += 32) {
                     uint32_t v[32];
@@ -498,7 +516,7 @@ static int env_int(const char* name, int dflt) {
 // Tuning overrides for experiments: CS_CONV_SW128=0 (use the plane kernel), CS_CONV_MT / CS_CONV_AS / CS_CONV_WS.
 static int conv1d_fwd_sw128(const void* x, const void* w, const float* bias, void* y, int B, int L, int Cin, int Cout, int K,
                             int pad, int relu, int Lout, cudaStream_t st) {
-    if (Cin % 64 != 0 || Cout % 32 != 0 || Lout + K - 1 <= 64 || !env_int("CS_CONV_SW128", 1)) return -1;
+    if (Cin % 64 != 0 || Cout % 32 != 0 || Lout + K - 1 <= 16 || !env_int("CS_CONV_SW128", 1)) return -1;
     Fwd128Shape s;
     s.B = B; s.L = L; s.Lout = Lout; s.Cin = Cin; s.Cout = Cout; s.K = K; s.pad = pad; s.relu = relu;
     s.NT = Cout % 128 == 0 ? 128 : (Cout % 64 == 0 ? 64 : 32);
@@ -506,6 +524,12 @@ static int conv1d_fwd_sw128(const void* x, const void* w, const float* bias, voi
     s.tile_stride = (s.R * 128 + 1023) & ~1023;
     s.tiles = (Lout + 127) / 128;
     s.total = B * s.tiles;
+    s.slot = 0;
+    if (Lout + K - 1 <= 64) {                                // short windows: whole samples packed into the 128-row tile
+        s.slot = Lout + K - 1 <= 32 ? 32 : 64;
+        s.tiles = 1;
+        s.total = (B + 128 / s.slot - 1) / (128 / s.slot);
+    }
     auto need = [&]() { return (size_t)2048 + (size_t)s.AS * s.tile_stride * s.MT + (size_t)s.WS * s.NT * 128; };
     // preferred: two co-resident CTAs per SM (256 TMEM columns and <= 113 KB shared memory each)
     const size_t kHalfSm = 113 * 1024, kFullSm = 227 * 1024;
@@ -533,9 +557,13 @@ static int conv1d_fwd_sw128(const void* x, const void* w, const float* bias, voi
     if (rc) return rc;
     rc = make_row_map(&mw, w, K, Cout, Cin, s.NT);
     if (rc) return rc;
-    CUtensorMap my = mw;
+    CUtensorMap my = mw, mxs = mx;
     if (s.tma_store) {
         rc = make_row_map(&my, y, B, Lout, Cout, 32);
+        if (rc) return rc;
+    }
+    if (s.slot) {
+        rc = make_row_map(&mxs, x, B, L, Cin, s.slot);
         if (rc) return rc;
     }
     const size_t smem = need();
@@ -548,7 +576,7 @@ static int conv1d_fwd_sw128(const void* x, const void* w, const float* bias, voi
     }
     const int units = (s.total + s.MT - 1) / s.MT, gy = units < 32768 ? units : 32768;
     dim3 grid(Cout / s.NT, gy, (units + gy - 1) / gy);
-    conv1d_fwd_sw128_kernel<<<grid, kFwdThreads, smem, st>>>(mx, mw, my, bias, (__nv_bfloat16*)y, s);
+    conv1d_fwd_sw128_kernel<<<grid, kFwdThreads, smem, st>>>(mx, mw, my, mxs, bias, (__nv_bfloat16*)y, s);
     CS_CUDA_OK(cudaGetLastError());
     return CS_OK;
 }
@@ -697,6 +725,188 @@ conv1d_wgrad_kernel(const __grid_constant__ CUtensorMap map_dy, const __grid_con
     (void)dbias;
 }
 
+// ------------------------------------------------------------------------------------------------
+// K3, wide-channel variant (Cin % 64 == 0 and Cout % 64 == 0): the same 128-byte swizzled rows as the forward
+// kernel.  A channels-last tile (row = position, 64 channels = 128 B) IS the MN-major SWIZZLE_128B operand
+// layout with the positions as the reduction dimension, so dy and x are used exactly as TMA delivers them:
+//   A = dy tile   [128 positions x 128 cout]  (two 64-channel blocks, LBO apart)      M = cout
+//   B = x tile    [R positions   x NC cin ]   (NC / 64 blocks), tap = start + tap * 128 B   N = cin
+// One TMEM accumulator [128 x NC] per tap, TP = 512 / NC taps per CTA.  grid = (cout tile, cin tile, tap group x
+// split of the (sample, position tile) list): all tap groups run in the same launch.
+// ------------------------------------------------------------------------------------------------
+constexpr int kWg128Stages = 3;
+struct Wg128Shape { int B, L, Lout, Cin, Cout, K, pad, TP, S, R, NC, x_block, tiles_per_sample, total_tiles, my_cout, slot; };
+
+__global__ void __launch_bounds__(kWgThreads, 1)
+conv1d_wgrad_sw128_kernel(const __grid_constant__ CUtensorMap map_dy, const __grid_constant__ CUtensorMap map_x,
+                          const __grid_constant__ CUtensorMap map_dys, const __grid_constant__ CUtensorMap map_xs,
+                          float* __restrict__ dw, Wg128Shape s) {
+    extern __shared__ uint8_t smem_raw[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int co0 = blockIdx.x * 128, ci0 = blockIdx.y * s.NC;
+    const int dy_alloc = 2 * 16384;                            // M = 128 always reads two 64-channel blocks
+    const int x_alloc = s.x_block * (s.NC / 64);
+    const int stage_bytes = dy_alloc + x_alloc;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw);
+    uint64_t* full = bars, *empty = bars + kWg128Stages, *acc_full = bars + 2 * kWg128Stages;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_full + 1);
+    uint8_t* ring = smem_raw + (((smem_u32(smem_raw) + 256 + 1023) & ~1023u) - smem_u32(smem_raw));
+    const uint32_t tmem_cols = 512;
+
+    // rows / blocks TMA never writes (Cout == 64; rows 128.. of a packed x tile) must hold finite values that meet
+    // zeros on the other operand: clear the ring once
+    if (s.my_cout < 128 || s.slot)
+        for (int i = threadIdx.x; i < kWg128Stages * stage_bytes / 16; i += kWgThreads)
+            reinterpret_cast<uint4*>(ring)[i] = make_uint4(0, 0, 0, 0);
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < kWg128Stages; ++i) { mbar_init(full + i, 1); mbar_init(empty + i, 1); }
+        mbar_init(acc_full, 1);
+        fence_mbar_init();
+        tma_prefetch_desc(&map_dy); tma_prefetch_desc(&map_x);
+    }
+    if (warp == 1) tmem_alloc(tmem_slot, tmem_cols);
+    fence_proxy_async_smem();
+    tc_fence_before_sync();
+    __syncthreads();
+    tc_fence_after_sync();
+    const uint32_t tmem_base = *tmem_slot;
+    const int split = blockIdx.z % s.S, k0 = (blockIdx.z / s.S) * s.TP;
+    const int ktaps = s.K - k0 < s.TP ? s.K - k0 : s.TP;
+    const int t_begin = (int)(((long long)s.total_tiles * split) / s.S);
+    const int t_end = (int)(((long long)s.total_tiles * (split + 1)) / s.S);
+    const int n_iter = t_end - t_begin;
+
+    if (warp == 0) {
+        if (elect_one()) {
+            const uint32_t tx = (uint32_t)(s.my_cout / 64) * 16384u + (uint32_t)(s.NC / 64) * s.R * 128u;
+            for (int it = 0; it < n_iter; ++it) {
+                const int tile = t_begin + it, b = tile / s.tiles_per_sample, l0 = (tile % s.tiles_per_sample) * 128;
+                const int sg = it % kWg128Stages;
+                if (it >= kWg128Stages) mbar_wait(empty + sg, ((it / kWg128Stages) - 1) & 1);
+                uint8_t* st = ring + sg * stage_bytes;
+                if (!s.slot) {
+                    mbar_arrive_expect_tx(full + sg, tx);
+                    for (int h = 0; h < s.my_cout / 64; ++h) tma_load_3d(st + h * 16384, &map_dy, full + sg, co0 + h * 64, l0, b);
+                    for (int h = 0; h < s.NC / 64; ++h)
+                        tma_load_3d(st + dy_alloc + h * s.x_block, &map_x, full + sg, ci0 + h * 64, l0 + k0 - s.pad, b);
+                } else {
+                    // packed short windows: `tile` is a group of 128/slot samples, one `slot`-row box each (dy rows past
+                    // Lout arrive as zeros, which is what keeps a sample's taps out of its neighbour)
+                    const int spt = 128 / s.slot;
+                    mbar_arrive_expect_tx(full + sg, (uint32_t)(s.my_cout / 64 + s.NC / 64) * 16384u);
+                    for (int j = 0; j < spt; ++j) {
+                        for (int h = 0; h < s.my_cout / 64; ++h)
+                            tma_load_3d(st + h * 16384 + j * s.slot * 128, &map_dys, full + sg, co0 + h * 64, 0, tile * spt + j);
+                        for (int h = 0; h < s.NC / 64; ++h)
+                            tma_load_3d(st + dy_alloc + h * s.x_block + j * s.slot * 128, &map_xs, full + sg, ci0 + h * 64,
+                                        k0 - s.pad, tile * spt + j);
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (elect_one()) {
+            const uint32_t idesc = idesc_f16(FMT_BF16, 128, s.NC, MAJOR_MN, MAJOR_MN);
+            for (int it = 0; it < n_iter; ++it) {
+                const int sg = it % kWg128Stages;
+                mbar_wait(full + sg, (it / kWg128Stages) & 1);
+                tc_fence_after_sync();
+                const uint32_t a_addr = smem_u32(ring + sg * stage_bytes), b_addr = a_addr + dy_alloc;
+                for (int c = 0; c < 8; ++c) {                   // 8 chunks of 16 positions (16 rows x 128 B = 2048 B)
+                    const uint64_t a = smem_desc_sw128_mn(a_addr + c * 2048, 16384, 1024);
+                    for (int k = 0; k < ktaps; ++k)
+                        mma_f16(tmem_base + k * s.NC, a, smem_desc_sw128_mn(b_addr + c * 2048 + k * 128, s.x_block, 1024), idesc,
+                                (it > 0 || c > 0) ? 1u : 0u);
+                }
+                mma_commit(empty + sg);
+            }
+            mma_commit(acc_full);
+        }
+    } else if (n_iter > 0) {
+        const int q = warp & 3;
+        mbar_wait(acc_full, 0);
+        tc_fence_after_sync();
+        const int co = co0 + q * 32 + lane;
+        for (int k = 0; k < ktaps; ++k) {
+            for (int c0 = 0; c0 < s.NC; c0 += 32) {
+                uint32_t v[32];
+                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + k * s.NC + c0, v);
+                tmem_ld_wait();
+                if (co < s.Cout) {
+                    float* dst = dw + ((size_t)(k0 + k) * s.Cout + co) * s.Cin + ci0 + c0;
+#pragma unroll
+                    for (int j = 0; j < 32; j += 4)
+                        asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + j), "f"(__uint_as_float(v[j])),
+                                     "f"(__uint_as_float(v[j + 1])), "f"(__uint_as_float(v[j + 2])), "f"(__uint_as_float(v[j + 3])) : "memory");
+                }
+            }
+        }
+    }
+    tc_fence_before_sync();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc(tmem_base, tmem_cols);
+}
+
+// returns -1 when the shape is outside this variant (the plane kernel handles it)
+static int conv1d_wgrad_sw128(const void* x, const void* dy, float* dw, int B, int L, int Cin, int Cout, int K, int pad, int Lout,
+                              cudaStream_t st) {
+    if (Cin % 64 != 0 || Cout % 64 != 0 || (Cout > 64 && Cout % 128 != 0) || Lout + K - 1 <= 16 || !env_int("CS_CONV_SW128", 1)) return -1;
+    Wg128Shape s;
+    memset(&s, 0, sizeof(s));
+    s.B = B; s.L = L; s.Lout = Lout; s.Cin = Cin; s.Cout = Cout; s.K = K; s.pad = pad;
+    s.tiles_per_sample = (Lout + 127) / 128; s.total_tiles = B * s.tiles_per_sample;
+    s.my_cout = Cout < 128 ? Cout : 128;
+    if (Lout + K - 1 <= 64) {                                // short windows: 128/slot whole samples per reduction tile
+        s.slot = Lout + K - 1 <= 32 ? 32 : 64;
+        s.tiles_per_sample = 1;
+        s.total_tiles = (B + 128 / s.slot - 1) / (128 / s.slot);
+    }
+    // 128 input channels per CTA halve the shared-memory operand bytes per FLOP (4 taps per pass); very wide filters
+    // are better off with 64 channels x 8 taps per pass (fewer passes over dy and x)
+    s.NC = (K <= 8 && Cin % 128 == 0) ? 128 : 64;
+    { const int v = env_int("CS_WGRAD_NC", 0); if ((v == 64 || v == 128) && Cin % v == 0) s.NC = v; }
+    s.TP = 512 / s.NC;
+    const int passes = (K + s.TP - 1) / s.TP;
+    const int gx = (Cout + 127) / 128, gy = Cin / s.NC, outs = gx * gy * passes;
+    // Split of the reduction (sample, tile) list.  Every split ends with an atomic flush of its [taps x 128 x NC]
+    // partial (256 KB at most), and all CTAs flush at about the same time, so the flush costs ~ splits * outs * c_epi
+    // while the MMA time falls as tiles / splits: take the minimum of the sum, capped at two CTAs per SM.
+    const double t_tile = 8.0 * (K < s.TP ? K : s.TP) * (s.NC / 2) / 1.7e3;     // us per tile (MMA issue bound, 1.7 GHz)
+    const double c_epi = 0.17;                                                    // us per flushed CTA (measured ~1.5 TB/s)
+    int splits = (int)(sqrt((double)s.total_tiles * t_tile / (outs * c_epi)) + 0.5);
+    { const int v = env_int("CS_WGRAD_SPLITS", 0); if (v > 0) splits = v; }
+    const int cap = (2 * num_sms() + outs - 1) / outs;
+    if (splits > cap) splits = cap;
+    if (splits > s.total_tiles) splits = s.total_tiles;
+    if (splits < 1) splits = 1;
+    s.S = splits;
+    s.R = 128 + (K < s.TP ? K : s.TP) - 1;
+    s.x_block = (s.R * 128 + 1023) & ~1023;
+    CUtensorMap mdy, mx;
+    int rc = make_row_map(&mdy, dy, B, Lout, Cout, 128);
+    if (rc) return rc;
+    rc = make_row_map(&mx, x, B, L, Cin, s.R);
+    if (rc) return rc;
+    CUtensorMap mdys = mdy, mxs = mx;
+    if (s.slot) {
+        rc = make_row_map(&mdys, dy, B, Lout, Cout, s.slot);
+        if (rc) return rc;
+        rc = make_row_map(&mxs, x, B, L, Cin, s.slot);
+        if (rc) return rc;
+    }
+    const size_t smem = 2048 + (size_t)kWg128Stages * (2 * 16384 + (size_t)s.x_block * (s.NC / 64));
+    static size_t configured[64] = {};
+    int dev = 0;
+    CS_CUDA_OK(cudaGetDevice(&dev));
+    if (smem > configured[dev & 63]) {
+        CS_CUDA_OK(cudaFuncSetAttribute(conv1d_wgrad_sw128_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured[dev & 63] = smem;
+    }
+    conv1d_wgrad_sw128_kernel<<<dim3(gx, gy, passes * splits), kWgThreads, smem, st>>>(mdy, mx, mdys, mxs, dw, s);
+    CS_CUDA_OK(cudaGetLastError());
+    return CS_OK;
+}
+
 // per-channel column sum of a channels-last bf16 tensor (bias gradient)
 __global__ void colsum_kernel(const __nv_bfloat162* __restrict__ x, float* __restrict__ out, int64_t rows, int C) {
     const int C2 = C >> 1;
@@ -735,7 +945,9 @@ int conv1d_wgrad(const void* x, const void* dy, float* dw, float* dbias, int B, 
         s.total_tiles = (B + 128 / s.slot - 1) / (128 / s.slot);
         if (splits > s.total_tiles) splits = s.total_tiles;
     }
-    for (int k0 = 0; k0 < K; k0 += kWgTapsPerPass) {
+    const int rc128 = conv1d_wgrad_sw128(x, dy, dw, B, L, Cin, Cout, K, pad, Lout, st);
+    if (rc128 > 0) return rc128;
+    for (int k0 = 0; rc128 < 0 && k0 < K; k0 += kWgTapsPerPass) {
         s.k0 = k0; s.ktaps = K - k0 < kWgTapsPerPass ? K - k0 : kWgTapsPerPass;
         s.R = s.slot ? ((128 + s.ktaps - 1 + 7) & ~7) : 128 + s.ktaps - 1;
         CUtensorMap mdy, mx;

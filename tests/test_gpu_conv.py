@@ -21,7 +21,8 @@ CASES = [(4, 500, 16, 16, 5, 2), (2, 360, 64, 128, 7, 3), (3, 130, 256, 256, 3, 
          # 128-byte-row (swizzled) operand path: wide taps, Cout tile of 32, ragged last tile
          (2, 500, 64, 64, 31, 15), (2, 200, 128, 96, 9, 4), (1, 513, 64, 256, 5, 2),
          # short windows: several samples packed into one 128-row tile (slot 64 / 32 / 16)
-         (6, 45, 64, 128, 7, 3), (3, 20, 32, 32, 5, 2), (19, 10, 16, 16, 3, 1), (5, 58, 256, 256, 7, 3), (64, 45, 768, 768, 7, 3)]
+         (6, 45, 64, 128, 7, 3), (3, 20, 32, 32, 5, 2), (19, 10, 16, 16, 3, 1), (5, 58, 256, 256, 7, 3), (64, 45, 768, 768, 7, 3),
+         (9, 24, 64, 64, 5, 2), (7, 30, 128, 256, 3, 1)]
 
 
 @pytest.mark.parametrize("B,L,Cin,Cout,K,pad", CASES)
