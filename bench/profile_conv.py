@@ -18,7 +18,7 @@ dw = torch.zeros(K, C, C, device=dev)
 _lib.check(lib.cs_conv1d_prepare_dgrad_weight(w.data_ptr(), wt.data_ptr(), K, C, C, st))
 for it in range(4):
     _lib.check(lib.cs_conv1d_fwd(x.data_ptr(), w.data_ptr(), None, y.data_ptr(), B, L, C, C, K, K // 2, 1, 0, st))
-    _lib.check(lib.cs_conv1d_dgrad(dy.data_ptr(), wt.data_ptr(), dx.data_ptr(), B, L, C, C, K, K // 2, 1, st))
+    _lib.check(lib.cs_conv1d_dgrad_direct(dy.data_ptr(), w.data_ptr(), dx.data_ptr(), B, L, C, C, K, K // 2, 1, st))
     _lib.check(lib.cs_conv1d_wgrad(x.data_ptr(), dy.data_ptr(), dw.data_ptr(), None, B, L, C, C, K, K // 2, 1, st))
 torch.cuda.synchronize()
 print("ok", float(y.float().abs().mean()), float(dw.abs().mean()))

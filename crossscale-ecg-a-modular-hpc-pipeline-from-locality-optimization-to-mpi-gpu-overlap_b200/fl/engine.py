@@ -149,6 +149,7 @@ class KernelLocalTrainer:
         # bf16 shadow of the whole arena, refreshed by the SGD kernel: conv layers read their weights from it
         # (no per-layer cast kernels) and accumulate weight gradients straight into the flat gradient arena
         from ..ops.conv1d import Conv1dB200
+        from ..ops.norm_act import BNReLU1d
         self.shadow = self.flat.flat.to(torch.bfloat16)
         for mod in model.modules():
             if isinstance(mod, Conv1dB200) and mod.cin > 1:
@@ -156,6 +157,8 @@ class KernelLocalTrainer:
                 off = self.flat.offsets[i]
                 mod.weight_bf16 = self.shadow[off:off + mod.weight.numel()].view_as(mod.weight)
                 mod.fused_wgrad = True
+            elif isinstance(mod, BNReLU1d):
+                mod.fused_grad = True                       # dgamma / dbeta are added into the arena by the reduction kernel
         self.sync = None
         if sync_grads:
             from ..parallel.grad_sync import GradSync

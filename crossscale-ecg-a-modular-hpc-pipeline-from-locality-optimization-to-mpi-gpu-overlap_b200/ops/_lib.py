@@ -36,6 +36,7 @@ _CUDA_SIGS = {
     "cs_sgd_momentum": (i32, [vp, vp, vp, i64, f32, f32, f32, i32, vp, vp, f32, f32, i32, vp, vp]),
     "cs_conv1d_fwd": (i32, [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, vp]),
     "cs_conv1d_dgrad": (i32, [vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp]),
+    "cs_conv1d_dgrad_direct": (i32, [vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp]),
     "cs_conv1d_prepare_dgrad_weight": (i32, [vp, vp, i32, i32, i32, vp]),
     "cs_conv1d_wgrad": (i32, [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp]),
     "cs_conv1d_cin1_fwd": (i32, [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp]),
@@ -45,6 +46,10 @@ _CUDA_SIGS = {
     "cs_bn_bwd_reduce": (i32, [vp, vp, vp, vp, vp, vp, vp, i64, i32, i32, vp]),
     "cs_bn_bwd_apply": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i64, i32, i32, vp]),
     "cs_bn_finalize": (i32, [vp, vp, vp, vp, vp, i32, i64, f32, f32, vp]),
+    "cs_bn_stats_finalize": (i32, [vp, vp, vp, vp, vp, vp, vp, i64, i32, f32, f32, vp, vp, vp, vp]),
+    "cs_bn_bwd_reduce_ws": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i64, i32, i32, vp]),
+    "cs_bn_apply_coef": (i32, [vp, vp, vp, vp, i64, i32, i32, vp]),
+    "cs_bn_bwd_apply_coef": (i32, [vp, vp, vp, vp, vp, vp, i64, i32, i32, vp]),
     "cs_avgpool2_fwd": (i32, [vp, vp, i32, i32, i32, vp]),
     "cs_avgpool2_bwd": (i32, [vp, vp, i32, i32, i32, vp]),
     "cs_avgpool_fwd": (i32, [vp, vp, i32, i32, i32, vp]),
@@ -143,6 +148,9 @@ def rt_lib() -> C.CDLL:
                 lib.cs_rendezvous_last_error.restype = C.c_char_p
                 _rt = lib
     return _rt
+
+
+CS_OK, CS_ERR_INVALID, CS_ERR_CUDA, CS_ERR_UNSUPPORTED = 0, 1, 2, 3      # include/crossscale.h
 
 
 def check(rc: int, what: str = "") -> None:

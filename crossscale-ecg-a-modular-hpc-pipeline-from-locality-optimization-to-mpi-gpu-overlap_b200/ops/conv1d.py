@@ -58,11 +58,14 @@ class _ConvNLC(torch.autograd.Function):
         k, cout, _ = w.shape
         dx = None
         if ctx.needs_input_grad[0]:
-            wt = torch.empty((k, cin, cout), dtype=torch.bfloat16, device=x.device)
-            _lib.check(lib.cs_conv1d_prepare_dgrad_weight(w.data_ptr(), wt.data_ptr(), k, cout, cin, st))
             dx = torch.empty_like(x)
-            _lib.check(lib.cs_conv1d_dgrad(dy.data_ptr(), wt.data_ptr(), dx.data_ptr(), b, l, cin, cout, k, pad, 1, st),
-                       "cs_conv1d_dgrad")
+            # wide layers: the data gradient reads the forward weights directly (MN-major operand, reversed taps)
+            rc = lib.cs_conv1d_dgrad_direct(dy.data_ptr(), w.data_ptr(), dx.data_ptr(), b, l, cin, cout, k, pad, 1, st)
+            if rc == _lib.CS_ERR_UNSUPPORTED:               # narrow layers: flipped / transposed copy + forward kernel
+                wt = torch.empty((k, cin, cout), dtype=torch.bfloat16, device=x.device)
+                _lib.check(lib.cs_conv1d_prepare_dgrad_weight(w.data_ptr(), wt.data_ptr(), k, cout, cin, st))
+                rc = lib.cs_conv1d_dgrad(dy.data_ptr(), wt.data_ptr(), dx.data_ptr(), b, l, cin, cout, k, pad, 1, st)
+            _lib.check(rc, "cs_conv1d_dgrad")
         fused = bool(getattr(module, "fused_wgrad", False)) and weight.grad is not None and weight.grad.is_contiguous() \
             and (bias is None or bias.grad is not None)
         if fused:                                           # reductions land directly in the gradient arena

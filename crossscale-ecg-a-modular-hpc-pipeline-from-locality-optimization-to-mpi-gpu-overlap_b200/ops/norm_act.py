@@ -15,53 +15,68 @@ from . import _lib
 
 
 class _BNAct(torch.autograd.Function):
+    """``ws`` is the layer's persistent workspace (fp32 [4C] accumulators + int32 ticket, see ``BNReLU1d``): the
+    reductions finish inside their own kernel (last block) and leave it zero again, so a training step runs
+    2 launches forward and 2 backward per layer with no fill / finalize / add kernels."""
+
     @staticmethod
-    def forward(ctx, x, gamma, beta, residual, relu, eps, mean_in, var_in, running, momentum):
+    def forward(ctx, x, gamma, beta, residual, relu, eps, mean_in, var_in, running, momentum, ws, module):
         lib, st = _lib.cuda_lib(), _lib.stream_ptr()
         x = x.contiguous()
         b, l, c = x.shape
         rows = b * l
-        if mean_in is None:                                # training: batch statistics + running update, 2 launches
-            buf = torch.zeros(4 * c, dtype=torch.float32, device=x.device)
-            stats, mean, rstd = buf[:2 * c], buf[2 * c:3 * c], buf[3 * c:]
-            _lib.check(lib.cs_bn_stats(x.data_ptr(), stats.data_ptr(), rows, c, st), "cs_bn_stats")
+        g32, b32 = gamma.detach().float().contiguous(), beta.detach().float().contiguous()
+        buf = torch.empty(4 * c, dtype=torch.float32, device=x.device)
+        mean, rstd, coef = buf[:c], buf[c:2 * c], buf[2 * c:]
+        if mean_in is None:                                # training: batch statistics + running update in one launch
             rm, rv = running if running is not None else (None, None)
-            _lib.check(lib.cs_bn_finalize(stats.data_ptr(), mean.data_ptr(), rstd.data_ptr(), _lib.ptr(rm), _lib.ptr(rv), c, rows,
-                                          float(eps), float(momentum), st), "cs_bn_finalize")
+            acc, ticket = ws
+            _lib.check(lib.cs_bn_stats_finalize(x.data_ptr(), acc.data_ptr(), ticket.data_ptr(), mean.data_ptr(), rstd.data_ptr(),
+                                                _lib.ptr(rm), _lib.ptr(rv), rows, c, float(eps), float(momentum),
+                                                g32.data_ptr(), b32.data_ptr(), coef.data_ptr(), st), "cs_bn_stats_finalize")
         else:
-            mean = mean_in.float().contiguous()
-            rstd = torch.rsqrt(var_in.float() + eps)
+            mean.copy_(mean_in.float())
+            rstd.copy_(torch.rsqrt(var_in.float() + eps))
+            coef[:c] = rstd * g32
+            coef[c:] = b32 - mean * coef[:c]
         res = None if residual is None else residual.contiguous()
         y = torch.empty_like(x)
-        g32, b32 = gamma.detach().float().contiguous(), beta.detach().float().contiguous()
-        _lib.check(lib.cs_bn_apply(x.data_ptr(), _lib.ptr(res), y.data_ptr(), mean.contiguous().data_ptr(),
-                                   rstd.contiguous().data_ptr(), g32.data_ptr(), b32.data_ptr(), rows, c, int(relu), st),
-                   "cs_bn_apply")
+        _lib.check(lib.cs_bn_apply_coef(x.data_ptr(), _lib.ptr(res), y.data_ptr(), coef.data_ptr(), rows, c, int(relu), st),
+                   "cs_bn_apply_coef")
         ctx.save_for_backward(x, y, mean, rstd, g32)
-        ctx.meta = (relu, residual is not None, mean_in is None)
+        ctx.meta = (relu, residual is not None, mean_in is None, ws, module)
+        ctx.params = (gamma, beta)
         return y
 
     @staticmethod
     def backward(ctx, dy):
-        x, y, mean, rstd, gamma = ctx.saved_tensors
-        relu, has_res, training = ctx.meta
+        x, y, mean, rstd, g32 = ctx.saved_tensors
+        relu, has_res, training, ws, module = ctx.meta
+        gamma, beta = ctx.params
         lib, st = _lib.cuda_lib(), _lib.stream_ptr()
         b, l, c = x.shape
         rows = b * l
         dy = dy.contiguous()
-        dgb = torch.zeros(2 * c, dtype=torch.float32, device=x.device)
-        dgamma, dbeta = dgb[:c], dgb[c:]
-        _lib.check(lib.cs_bn_bwd_reduce(x.data_ptr(), y.data_ptr(), dy.data_ptr(), mean.data_ptr(), rstd.data_ptr(),
-                                        dgamma.data_ptr(), dbeta.data_ptr(), rows, c, int(relu), st), "cs_bn_bwd_reduce")
+        buf = torch.empty(5 * c, dtype=torch.float32, device=x.device)
+        dgamma, dbeta, coef = buf[:c], buf[c:2 * c], buf[2 * c:]
+        # a trainer that owns a flat gradient arena lets the kernel add the sums straight into gamma.grad / beta.grad
+        # (autograd still fires the parameters' post-accumulate-grad hooks when None is returned for them)
+        fused = bool(getattr(module, "fused_grad", False)) and gamma.grad is not None and beta.grad is not None \
+            and gamma.grad.is_contiguous() and beta.grad.is_contiguous() and gamma.grad.dtype == torch.float32
+        acc, ticket = ws
+        _lib.check(lib.cs_bn_bwd_reduce_ws(x.data_ptr(), y.data_ptr(), dy.data_ptr(), mean.data_ptr(), rstd.data_ptr(),
+                                           acc[2 * c:].data_ptr(), ticket[1:].data_ptr(), dgamma.data_ptr(), dbeta.data_ptr(),
+                                           gamma.grad.data_ptr() if fused else None, beta.grad.data_ptr() if fused else None,
+                                           g32.data_ptr(), coef.data_ptr(), rows, c, int(relu), st), "cs_bn_bwd_reduce_ws")
+        if not training:                                    # fixed statistics: the batch-correction terms vanish
+            coef[c:].zero_()
         dx = torch.empty_like(x)
         dres = torch.empty_like(x) if has_res else None
-        # eval mode (fixed statistics): the correction terms vanish -> pass zeros for the reductions
-        zg = dgamma if training else torch.zeros_like(dgamma)
-        zb = dbeta if training else torch.zeros_like(dbeta)
-        _lib.check(lib.cs_bn_bwd_apply(x.data_ptr(), y.data_ptr(), dy.data_ptr(), mean.data_ptr(), rstd.data_ptr(),
-                                       gamma.data_ptr(), zg.data_ptr(), zb.data_ptr(), dx.data_ptr(), _lib.ptr(dres),
-                                       rows, c, int(relu), st), "cs_bn_bwd_apply")
-        return dx, dgamma, dbeta, dres, None, None, None, None, None, None
+        _lib.check(lib.cs_bn_bwd_apply_coef(x.data_ptr(), y.data_ptr(), dy.data_ptr(), coef.data_ptr(), dx.data_ptr(),
+                                            _lib.ptr(dres), rows, c, int(relu), st), "cs_bn_bwd_apply_coef")
+        if fused:
+            return dx, None, None, dres, None, None, None, None, None, None, None, None
+        return dx, dgamma, dbeta, dres, None, None, None, None, None, None, None, None
 
 
 class BNReLU1d(nn.Module):
@@ -74,6 +89,14 @@ class BNReLU1d(nn.Module):
         self.bias = nn.Parameter(torch.zeros(channels))
         self.register_buffer("running_mean", torch.zeros(channels))
         self.register_buffer("running_var", torch.ones(channels))
+        self.fused_grad = False          # accumulate dgamma / dbeta into .grad inside the reduction kernel
+        self._ws = None                  # (fp32 [4C] accumulators, int32 [2] tickets): zero, and left zero by every kernel
+
+    def _workspace(self, device):
+        if self._ws is None or self._ws[0].device != device:
+            c = self.weight.numel()
+            self._ws = (torch.zeros(4 * c, dtype=torch.float32, device=device), torch.zeros(2, dtype=torch.int32, device=device))
+        return self._ws
 
     def forward(self, x: torch.Tensor, residual: Optional[torch.Tensor] = None) -> torch.Tensor:
         if not x.is_cuda:
@@ -82,11 +105,12 @@ class BNReLU1d(nn.Module):
             if residual is not None:
                 y = y + residual
             return F.relu(y) if self.relu else y
+        ws = self._workspace(x.device)
         if self.training:
             return _BNAct.apply(x, self.weight, self.bias, residual, self.relu, self.eps, None, None,
-                                (self.running_mean, self.running_var), self.momentum)
+                                (self.running_mean, self.running_var), self.momentum, ws, self)
         return _BNAct.apply(x, self.weight, self.bias, residual, self.relu, self.eps, self.running_mean, self.running_var,
-                            None, self.momentum)
+                            None, self.momentum, ws, self)
 
 
 class _GlobalAvgPool(torch.autograd.Function):

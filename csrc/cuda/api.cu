@@ -41,6 +41,10 @@ int cross_entropy(const float*, const int64_t*, int, int, const float*, float*, 
 int sgd_momentum(float*, float*, const float*, int64_t, float, float, float, int, int32_t*, float*, float, float, int, void*, cudaStream_t);
 int zscore_rows(const float*, void*, int, int, int, cudaStream_t);
 int bn_stats(const void*, float*, int64_t, int, cudaStream_t);
+int bn_stats_finalize(const void*, float*, int32_t*, float*, float*, float*, float*, int64_t, int, float, float, const float*, const float*, float*, cudaStream_t);
+int bn_bwd_reduce_ws(const void*, const void*, const void*, const float*, const float*, float*, int32_t*, float*, float*, float*, float*, const float*, float*, int64_t, int, int, cudaStream_t);
+int bn_apply_coef(const void*, const void*, void*, const float*, int64_t, int, int, cudaStream_t);
+int bn_bwd_apply_coef(const void*, const void*, const void*, const float*, void*, void*, int64_t, int, int, cudaStream_t);
 int bn_apply(const void*, const void*, void*, const float*, const float*, const float*, const float*, int64_t, int, int, cudaStream_t);
 int bn_bwd_reduce(const void*, const void*, const void*, const float*, const float*, float*, float*, int64_t, int, int, cudaStream_t);
 int bn_bwd_apply(const void*, const void*, const void*, const float*, const float*, const float*, const float*, const float*, void*, void*, int64_t, int, int, cudaStream_t);
@@ -69,6 +73,7 @@ void* comm_arena(cs_comm*, int);
 size_t comm_bytes(cs_comm*);
 
 int conv1d_fwd(const void*, const void*, const float*, void*, int, int, int, int, int, int, int, int, cudaStream_t);
+int conv1d_dgrad_direct(const void*, const void*, void*, int, int, int, int, int, int, cudaStream_t);
 int conv1d_prepare_dgrad_weight(const void*, void*, int, int, int, cudaStream_t);
 int conv1d_wgrad(const void*, const void*, float*, float*, int, int, int, int, int, int, int, cudaStream_t);
 int conv1d_cin1_fwd(const float*, const float*, const float*, void*, int, int, int, int, int, int, int, cudaStream_t);
@@ -167,6 +172,11 @@ int cs_conv1d_dgrad(const void* dy, const void* wt, void* dx, int B, int L, int 
     const int Lout = L + 2 * pad - K + 1;
     return conv1d_fwd(dy, wt, nullptr, dx, B, Lout, Cout, Cin, K, K - 1 - pad, 1, 0, ST(s));
 }
+int cs_conv1d_dgrad_direct(const void* dy, const void* w, void* dx, int B, int L, int Cin, int Cout, int K, int pad,
+                           int stride, cs_stream_t s) {
+    if (stride != 1) return CS_ERR_UNSUPPORTED;
+    return conv1d_dgrad_direct(dy, w, dx, B, L, Cin, Cout, K, pad, ST(s));
+}
 int cs_conv1d_prepare_dgrad_weight(const void* w, void* wt, int K, int Cout, int Cin, cs_stream_t s) {
     return conv1d_prepare_dgrad_weight(w, wt, K, Cout, Cin, ST(s));
 }
@@ -196,6 +206,24 @@ int cs_bn_bwd_apply(const void* x, const void* y, const void* dy, const float* m
                     const float* gamma, const float* dgamma, const float* dbeta, void* dx, void* dres, int64_t rows,
                     int C, int relu, cs_stream_t s) {
     return bn_bwd_apply(x, y, dy, mean, rstd, gamma, dgamma, dbeta, dx, dres, rows, C, relu, ST(s));
+}
+int cs_bn_stats_finalize(const void* x, float* acc, int32_t* ticket, float* mean, float* rstd, float* running_mean,
+                         float* running_var, int64_t rows, int C, float eps, float momentum, const float* gamma,
+                         const float* beta, float* coef, cs_stream_t s) {
+    return bn_stats_finalize(x, acc, ticket, mean, rstd, running_mean, running_var, rows, C, eps, momentum, gamma, beta, coef, ST(s));
+}
+int cs_bn_bwd_reduce_ws(const void* x, const void* y, const void* dy, const float* mean, const float* rstd, float* acc,
+                        int32_t* ticket, float* dgamma, float* dbeta, float* gamma_grad, float* beta_grad, const float* gamma,
+                        float* coef, int64_t rows, int C, int relu, cs_stream_t s) {
+    return bn_bwd_reduce_ws(x, y, dy, mean, rstd, acc, ticket, dgamma, dbeta, gamma_grad, beta_grad, gamma, coef, rows, C, relu,
+                            ST(s));
+}
+int cs_bn_apply_coef(const void* x, const void* res, void* y, const float* coef, int64_t rows, int C, int relu, cs_stream_t s) {
+    return bn_apply_coef(x, res, y, coef, rows, C, relu, ST(s));
+}
+int cs_bn_bwd_apply_coef(const void* x, const void* y, const void* dy, const float* coef, void* dx, void* dres, int64_t rows,
+                         int C, int relu, cs_stream_t s) {
+    return bn_bwd_apply_coef(x, y, dy, coef, dx, dres, rows, C, relu, ST(s));
 }
 int cs_bn_finalize(const float* stats, float* mean, float* rstd, float* running_mean, float* running_var, int C, int64_t rows,
                    float eps, float momentum, cs_stream_t s) {

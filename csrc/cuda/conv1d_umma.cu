@@ -219,7 +219,7 @@ conv1d_fwd_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
 }
 
 static int conv1d_fwd_sw128(const void* x, const void* w, const float* bias, void* y, int B, int L, int Cin, int Cout, int K,
-                            int pad, int relu, int Lout, cudaStream_t st);
+                            int pad, int relu, int Lout, cudaStream_t st, int wmn = 0);
 static int pick_ck(int C) { return C % 64 == 0 ? 64 : (C % 32 == 0 ? 32 : 16); }
 static int pick_nt(int C) { return C % 128 == 0 ? 128 : (C % 64 == 0 ? 64 : (C % 32 == 0 ? 32 : 16)); }
 
@@ -303,6 +303,8 @@ struct Fwd128Shape {
     int tiles, total;        // tiles per sample, B * tiles
     int tile_stride;         // bytes between the MT A tiles of one stage (multiple of 1024)
     int tma_store;           // epilogue through shared memory + TMA store (NT % 64 == 0)
+    int wmn;                 // 1: data gradient straight from the forward weights w[K][red][N] (N contiguous): the weight tile
+                             // is an MN-major B operand and the taps are read in reverse — no transposed copy of w
     int slot;                // 0, or 32 / 64: short windows (Lout + K - 1 <= slot), a tile packs 128/slot whole samples, each
                              // in its own `slot` rows (the taps of one sample never reach the next sample's outputs)
 };
@@ -389,14 +391,19 @@ conv1d_fwd_sw128_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_
                     const int sw = wi % s.WS;
                     if (wi >= s.WS) mbar_wait(empty_w + sw, ((wi / s.WS) - 1) & 1);
                     mbar_arrive_expect_tx(full_w + sw, w_bytes);
-                    tma_load_3d(w_ring + sw * w_bytes, &map_w, full_w + sw, c * 64, n0, k);
+                    if (!s.wmn) {
+                        tma_load_3d(w_ring + sw * w_bytes, &map_w, full_w + sw, c * 64, n0, k);
+                    } else {
+                        for (int h = 0; h < s.NT / 64; ++h)     // 64 reduction rows x 64 output channels per box
+                            tma_load_3d(w_ring + sw * w_bytes + h * 8192, &map_w, full_w + sw, n0 + h * 64, c * 64, s.K - 1 - k);
+                    }
                 }
             }
         }
     } else if (warp == 1) {
         // ===== MMA issuer =====
         if (elect_one()) {
-            const uint32_t idesc = idesc_f16(FMT_BF16, 128, s.NT, MAJOR_K, MAJOR_K);
+            const uint32_t idesc = idesc_f16(FMT_BF16, 128, s.NT, MAJOR_K, s.wmn ? MAJOR_MN : MAJOR_K);
             int wi = 0;
             uint32_t first = 1;
             for (int c = 0; c < chunks; ++c) {
@@ -408,13 +415,17 @@ conv1d_fwd_sw128_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_
                     const int sw = wi % s.WS;
                     mbar_wait(full_w + sw, (wi / s.WS) & 1);
                     tc_fence_after_sync();
-                    const uint64_t b0 = smem_desc_sw128(smem_u32(w_ring + sw * w_bytes), 1024);
+                    const uint32_t w_addr = smem_u32(w_ring + sw * w_bytes);
 #pragma unroll
                     for (int j = 0; j < 4; ++j) {            // 4 x 16 channels inside the 128-byte row
+                        // K-major weights: 16-channel step = 32 B inside the row.  MN-major (data gradient): the 16
+                        // reduction channels are 16 rows (2048 B) and the 64-channel output blocks sit 8192 B apart.
+                        const uint64_t bd = s.wmn ? smem_desc_sw128_mn(w_addr + j * 2048, 8192, 1024)
+                                                  : smem_desc_sw128(w_addr + j * 32, 1024);
                         for (int i = 0; i < s.MT; ++i) {
                             // tap k = k rows (k * 128 B) further down the tile; 16-channel step = 32 B inside the row
                             const uint64_t a = smem_desc_sw128(a_addr + i * s.tile_stride + k * 128 + j * 32, 1024);
-                            mma_f16(tmem_base + i * s.NT, a, b0 + (uint64_t)(j * 2), idesc, (first && j == 0) ? 0u : 1u);
+                            mma_f16(tmem_base + i * s.NT, a, bd, idesc, (first && j == 0) ? 0u : 1u);
                         }
                     }
                     first = 0;
@@ -515,9 +526,11 @@ static int env_int(const char* name, int dflt) {
 // Launches the 128-byte-row variant and returns CS_OK (or an error), or -1 when the shape is not one it covers.
 // Tuning overrides for experiments: CS_CONV_SW128=0 (use the plane kernel), CS_CONV_MT / CS_CONV_AS / CS_CONV_WS.
 static int conv1d_fwd_sw128(const void* x, const void* w, const float* bias, void* y, int B, int L, int Cin, int Cout, int K,
-                            int pad, int relu, int Lout, cudaStream_t st) {
+                            int pad, int relu, int Lout, cudaStream_t st, int wmn) {
     if (Cin % 64 != 0 || Cout % 32 != 0 || Lout + K - 1 <= 16 || !env_int("CS_CONV_SW128", 1)) return -1;
+    if (wmn && Cout % 64 != 0) return -1;
     Fwd128Shape s;
+    s.wmn = wmn;
     s.B = B; s.L = L; s.Lout = Lout; s.Cin = Cin; s.Cout = Cout; s.K = K; s.pad = pad; s.relu = relu;
     s.NT = Cout % 128 == 0 ? 128 : (Cout % 64 == 0 ? 64 : 32);
     s.R = 128 + K - 1;
@@ -534,6 +547,8 @@ static int conv1d_fwd_sw128(const void* x, const void* w, const float* bias, voi
     // preferred: two co-resident CTAs per SM (256 TMEM columns and <= 113 KB shared memory each)
     const size_t kHalfSm = 113 * 1024, kFullSm = 227 * 1024;
     s.MT = 256 / s.NT; if (s.MT > 4) s.MT = 4; if (s.MT > s.total) s.MT = s.total;
+    // small problems: fewer tiles per CTA so that every SM gets work (weights are re-streamed from L2, which is cheap here)
+    while (s.MT > 1 && (long long)(Cout / s.NT) * ((s.total + s.MT - 1) / s.MT) < 2LL * num_sms()) s.MT >>= 1;
     s.AS = 2; s.WS = 4;
     while (need() > kHalfSm && s.WS > 2) --s.WS;
     if (need() > kHalfSm) {                                  // wide taps: one activation stage, the sibling CTA covers the bubble
@@ -555,7 +570,7 @@ static int conv1d_fwd_sw128(const void* x, const void* w, const float* bias, voi
     CUtensorMap mx, mw;
     int rc = make_row_map(&mx, x, B, L, Cin, s.R);
     if (rc) return rc;
-    rc = make_row_map(&mw, w, K, Cout, Cin, s.NT);
+    rc = wmn ? make_row_map(&mw, w, K, Cin, Cout, 64) : make_row_map(&mw, w, K, Cout, Cin, s.NT);
     if (rc) return rc;
     CUtensorMap my = mw, mxs = mx;
     if (s.tma_store) {
@@ -579,6 +594,16 @@ static int conv1d_fwd_sw128(const void* x, const void* w, const float* bias, voi
     conv1d_fwd_sw128_kernel<<<grid, kFwdThreads, smem, st>>>(mx, mw, my, mxs, bias, (__nv_bfloat16*)y, s);
     CS_CUDA_OK(cudaGetLastError());
     return CS_OK;
+}
+
+// dx = conv(dy, flipped/transposed w) computed from the forward weights themselves (see Fwd128Shape::wmn).
+// CS_ERR_UNSUPPORTED (no error text) when the shape needs the transposed copy + conv1d_fwd instead.
+int conv1d_dgrad_direct(const void* dy, const void* w, void* dx, int B, int L, int Cin, int Cout, int K, int pad, cudaStream_t st) {
+    CS_REQUIRE(K >= 1 && K <= 64 && pad >= 0 && pad < K, "conv1d_dgrad: bad K=%d pad=%d", K, pad);
+    CS_REQUIRE((((uintptr_t)dy | (uintptr_t)w | (uintptr_t)dx) & 15) == 0, "conv1d_dgrad: pointers must be 16-byte aligned");
+    const int Lout = L + 2 * pad - K + 1;
+    const int rc = conv1d_fwd_sw128(dy, w, nullptr, dx, B, Lout, Cout, Cin, K, K - 1 - pad, 0, L, st, 1);
+    return rc < 0 ? CS_ERR_UNSUPPORTED : rc;
 }
 
 // w [K][Cout][Cin] -> wt [K][Cin][Cout] with taps flipped: wt[K-1-k][ci][co] = w[k][co][ci]
@@ -875,8 +900,12 @@ static int conv1d_wgrad_sw128(const void* x, const void* dy, float* dw, int B, i
     const double c_epi = 0.17;                                                    // us per flushed CTA (measured ~1.5 TB/s)
     int splits = (int)(sqrt((double)s.total_tiles * t_tile / (outs * c_epi)) + 0.5);
     { const int v = env_int("CS_WGRAD_SPLITS", 0); if (v > 0) splits = v; }
-    const int cap = (2 * num_sms() + outs - 1) / outs;
-    if (splits > cap) splits = cap;
+    // whole waves: one CTA per SM is resident (all of TMEM), so outs * splits should sit just under 1x or 2x the SM count
+    const int one_wave = num_sms() / outs > 0 ? num_sms() / outs : 1, two_waves = (2 * num_sms()) / outs > 0 ? (2 * num_sms()) / outs : 1;
+    if (env_int("CS_WGRAD_SPLITS", 0) <= 0) {
+        if (splits >= two_waves) splits = two_waves;
+        else if (splits > one_wave) splits = (2 * splits > 3 * one_wave) ? two_waves : one_wave;
+    }
     if (splits > s.total_tiles) splits = s.total_tiles;
     if (splits < 1) splits = 1;
     s.S = splits;

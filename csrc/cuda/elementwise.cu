@@ -244,7 +244,35 @@ __device__ __forceinline__ void column_reduce_finish(float (&acc)[Q][8], float* 
     }
 }
 
-__global__ void __launch_bounds__(kRedThreads) bn_stats_kernel(const uint4* __restrict__ x, float* __restrict__ stats, int64_t rows, int C) {
+// Optional tail of the two column reductions below, run by the LAST block to arrive (ticket): the per-channel totals
+// are complete in `acc` (L2 atomics), so that block turns them into the layer's outputs and then CLEARS acc and the
+// ticket — the accumulator is a persistent, self-cleaning workspace and no fill / finalize / add launches are needed.
+struct BnStatsTail {
+    int32_t* ticket;          // nullptr: plain accumulate-only kernel (cs_bn_stats / cs_bn_bwd_reduce)
+    float* mean; float* rstd; float* running_mean; float* running_var;
+    float rows, eps, momentum;
+    const float* gamma; const float* beta; float* coef;   // optional: coef[0:C] = rstd*gamma, coef[C:2C] = beta - mean*rstd*gamma
+};
+struct BnBwdTail {
+    int32_t* ticket;
+    float* dgamma; float* dbeta;          // this batch's reductions
+    float* gamma_grad; float* beta_grad;  // optional: += into the parameter gradient arena
+    const float* gamma; float* coef;      // optional: dx = a*d + p*x + q per channel, coef = [a | p | q] (3C)
+    float inv_rows;
+};
+
+__device__ __forceinline__ bool last_block_arrives(int32_t* ticket) {
+    __shared__ int is_last;
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) is_last = (atomicAdd(ticket, 1) == (int)gridDim.x - 1);
+    __syncthreads();
+    if (is_last) __threadfence();
+    return is_last != 0;
+}
+
+__global__ void __launch_bounds__(kRedThreads) bn_stats_kernel(const uint4* __restrict__ x, float* __restrict__ stats, int64_t rows, int C,
+                                                               BnStatsTail t) {
     extern __shared__ float sm_red[];
     const int G = C >> 3, rpb = kRedThreads / G;
     const int g = threadIdx.x % G, rl = threadIdx.x / G;
@@ -267,6 +295,24 @@ __global__ void __launch_bounds__(kRedThreads) bn_stats_kernel(const uint4* __re
     }
     float* const out[2] = {stats, stats + C};
     column_reduce_finish<2>(acc, out, C, g, rl, rpb, sm_red);
+    if (t.ticket == nullptr || !last_block_arrives(t.ticket)) return;
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+        const float m = __ldcg(stats + c) / t.rows;
+        const float var = fmaxf(__ldcg(stats + C + c) / t.rows - m * m, 0.0f);
+        t.mean[c] = m;
+        t.rstd[c] = rsqrtf(var + t.eps);
+        if (t.running_mean) {
+            t.running_mean[c] += t.momentum * (m - t.running_mean[c]);
+            t.running_var[c] += t.momentum * (var * (t.rows / fmaxf(t.rows - 1.0f, 1.0f)) - t.running_var[c]);
+        }
+        if (t.coef) {
+            const float sc = rsqrtf(var + t.eps) * t.gamma[c];
+            t.coef[c] = sc;
+            t.coef[C + c] = t.beta[c] - m * sc;
+        }
+        stats[c] = 0.0f; stats[C + c] = 0.0f;
+    }
+    if (threadIdx.x == 0) *t.ticket = 0;
 }
 
 __global__ void bn_apply_kernel(const uint4* __restrict__ x, const uint4* __restrict__ res, uint4* __restrict__ y,
@@ -292,7 +338,7 @@ __global__ void bn_apply_kernel(const uint4* __restrict__ x, const uint4* __rest
 __global__ void __launch_bounds__(kRedThreads) bn_bwd_reduce_kernel(const uint4* __restrict__ x, const uint4* __restrict__ y,
                                                                     const uint4* __restrict__ dy, const float* __restrict__ mean,
                                                                     const float* __restrict__ rstd, float* __restrict__ dgamma,
-                                                                    float* __restrict__ dbeta, int64_t rows, int C, int relu) {
+                                                                    float* __restrict__ dbeta, int64_t rows, int C, int relu, BnBwdTail t) {
     extern __shared__ float sm_red[];
     const int G = C >> 3, rpb = kRedThreads / G;
     const int g = threadIdx.x % G, rl = threadIdx.x / G;
@@ -327,6 +373,22 @@ __global__ void __launch_bounds__(kRedThreads) bn_bwd_reduce_kernel(const uint4*
     }
     float* const out[2] = {dgamma, dbeta};
     column_reduce_finish<2>(acc, out, C, g, rl, rpb, sm_red);
+    if (t.ticket == nullptr || !last_block_arrives(t.ticket)) return;
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {      // here dgamma / dbeta are the persistent accumulators
+        const float dg = __ldcg(dgamma + c), db = __ldcg(dbeta + c);
+        t.dgamma[c] = dg; t.dbeta[c] = db;
+        if (t.gamma_grad) { t.gamma_grad[c] += dg; t.beta_grad[c] += db; }
+        if (t.coef) {
+            // dx = gamma*rstd*(d - (dbeta + xhat*dgamma)/n), xhat = (x - mean)*rstd   ->   a*d + p*x + q
+            const float a = t.gamma[c] * rstd[c];
+            const float pc = -a * t.inv_rows * dg * rstd[c];
+            t.coef[c] = a;
+            t.coef[C + c] = pc;
+            t.coef[2 * C + c] = -a * t.inv_rows * db - pc * mean[c];
+        }
+        dgamma[c] = 0.0f; dbeta[c] = 0.0f;
+    }
+    if (threadIdx.x == 0) *t.ticket = 0;
 }
 
 __global__ void bn_bwd_apply_kernel(const uint4* __restrict__ x, const uint4* __restrict__ y, const uint4* __restrict__ dy,
@@ -353,6 +415,109 @@ __global__ void bn_bwd_apply_kernel(const uint4* __restrict__ x, const uint4* __
     }
 }
 
+// Coefficient forms of the two elementwise passes: a thread owns one 8-channel group, loads its per-channel
+// coefficients ONCE (vector loads) and then streams rows with four independent 16-byte loads in flight.
+__device__ __forceinline__ void load8(const float* p, float (&f)[8]) {
+    const float4 a = __ldg(reinterpret_cast<const float4*>(p)), b = __ldg(reinterpret_cast<const float4*>(p) + 1);
+    f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w; f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
+}
+
+__global__ void __launch_bounds__(kRedThreads) bn_apply_coef_kernel(const uint4* __restrict__ x, const uint4* __restrict__ res,
+                                                                    uint4* __restrict__ y, const float* __restrict__ coef,
+                                                                    int64_t rows, int C, int relu) {
+    const int G = C >> 3, rpb = kRedThreads / G;
+    const int g = threadIdx.x % G, rl = threadIdx.x / G;
+    if (rl >= rpb) return;
+    float sc[8], sh[8];
+    load8(coef + g * 8, sc); load8(coef + C + g * 8, sh);
+    const int64_t stride = (int64_t)gridDim.x * rpb;
+    for (int64_t r = (int64_t)blockIdx.x * rpb + rl; r < rows; r += 4 * stride) {
+        uint4 v[4], w[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int64_t rr = r + u * stride;
+            if (rr < rows) { v[u] = __ldg(x + rr * G + g); if (res) w[u] = __ldg(res + rr * G + g); }
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int64_t rr = r + u * stride;
+            if (rr < rows) {
+                float f[8], q[8];
+                unpack8(v[u], f);
+                if (res) unpack8(w[u], q);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    float o = fmaf(f[j], sc[j], sh[j]);
+                    if (res) o += q[j];
+                    f[j] = relu ? fmaxf(o, 0.0f) : o;
+                }
+                y[rr * G + g] = pack8(f);
+            }
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kRedThreads) bn_bwd_apply_coef_kernel(const uint4* __restrict__ x, const uint4* __restrict__ y,
+                                                                        const uint4* __restrict__ dy, const float* __restrict__ coef,
+                                                                        uint4* __restrict__ dx, uint4* __restrict__ dres,
+                                                                        int64_t rows, int C, int relu) {
+    const int G = C >> 3, rpb = kRedThreads / G;
+    const int g = threadIdx.x % G, rl = threadIdx.x / G;
+    if (rl >= rpb) return;
+    float a[8], p[8], q[8];
+    load8(coef + g * 8, a); load8(coef + C + g * 8, p); load8(coef + 2 * C + g * 8, q);
+    const int64_t stride = (int64_t)gridDim.x * rpb;
+    for (int64_t r = (int64_t)blockIdx.x * rpb + rl; r < rows; r += 2 * stride) {
+        uint4 vx[2], vy[2], vd[2];
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+            const int64_t rr = r + u * stride;
+            if (rr < rows) { vx[u] = __ldg(x + rr * G + g); vd[u] = __ldg(dy + rr * G + g); if (relu) vy[u] = __ldg(y + rr * G + g); }
+        }
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+            const int64_t rr = r + u * stride;
+            if (rr < rows) {
+                float fx[8], fd[8], fy[8];
+                unpack8(vx[u], fx); unpack8(vd[u], fd);
+                if (relu) {
+                    unpack8(vy[u], fy);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) if (fy[j] <= 0.0f) fd[j] = 0.0f;
+                }
+                if (dres) dres[rr * G + g] = pack8(fd);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) fx[j] = fmaf(a[j], fd[j], fmaf(p[j], fx[j], q[j]));
+                dx[rr * G + g] = pack8(fx);
+            }
+        }
+    }
+}
+
+static int stream_grid(int64_t rows, int rpb, int unroll) {
+    int64_t want = (rows + (int64_t)rpb * unroll - 1) / ((int64_t)rpb * unroll);
+    const int64_t cap = (int64_t)num_sms() * 8;
+    if (want > cap) want = cap;
+    return (int)(want < 1 ? 1 : want);
+}
+
+int bn_apply_coef(const void* x, const void* res, void* y, const float* coef, int64_t rows, int C, int relu, cudaStream_t st) {
+    CS_REQUIRE(C >= 8 && C % 8 == 0 && C <= 2048, "bn_apply: C=%d must be a multiple of 8 and <= 2048", C);
+    bn_apply_coef_kernel<<<stream_grid(rows, kRedThreads / (C / 8), 4), kRedThreads, 0, st>>>((const uint4*)x, (const uint4*)res,
+                                                                                             (uint4*)y, coef, rows, C, relu);
+    CS_CUDA_OK(cudaGetLastError());
+    return CS_OK;
+}
+
+int bn_bwd_apply_coef(const void* x, const void* y, const void* dy, const float* coef, void* dx, void* dres, int64_t rows, int C,
+                      int relu, cudaStream_t st) {
+    CS_REQUIRE(C >= 8 && C % 8 == 0 && C <= 2048, "bn_bwd: C=%d must be a multiple of 8 and <= 2048", C);
+    bn_bwd_apply_coef_kernel<<<stream_grid(rows, kRedThreads / (C / 8), 2), kRedThreads, 0, st>>>(
+        (const uint4*)x, (const uint4*)y, (const uint4*)dy, coef, (uint4*)dx, (uint4*)dres, rows, C, relu);
+    CS_CUDA_OK(cudaGetLastError());
+    return CS_OK;
+}
+
 static int red_grid(int64_t rows, int rpb, int unroll) {
     int64_t want = (rows + (int64_t)rpb * unroll * 4 - 1) / ((int64_t)rpb * unroll * 4);   // >= 4 passes per thread
     const int64_t cap = num_sms();
@@ -369,7 +534,22 @@ int bn_stats(const void* x, float* stats, int64_t rows, int C, cudaStream_t st) 
     CS_REQUIRE(C >= 8 && C % 8 == 0 && C <= 2048, "bn_stats: C=%d must be a multiple of 8 and <= 2048", C);
     const int rpb = kRedThreads / (C / 8);
     const size_t smem = (size_t)rpb * 2 * C * sizeof(float);
-    bn_stats_kernel<<<red_grid(rows, rpb, 4), kRedThreads, smem, st>>>((const uint4*)x, stats, rows, C);
+    bn_stats_kernel<<<red_grid(rows, rpb, 4), kRedThreads, smem, st>>>((const uint4*)x, stats, rows, C, BnStatsTail{});
+    CS_CUDA_OK(cudaGetLastError());
+    return CS_OK;
+}
+
+// statistics + finalize in ONE launch.  `acc` [2C] fp32 and `ticket` [1] int32 form a persistent workspace that must
+// be zero before the first call; the kernel leaves both zero again.
+int bn_stats_finalize(const void* x, float* acc, int32_t* ticket, float* mean, float* rstd, float* rm, float* rv, int64_t rows, int C,
+                      float eps, float momentum, const float* gamma, const float* beta, float* coef, cudaStream_t st) {
+    CS_REQUIRE(C >= 8 && C % 8 == 0 && C <= 2048, "bn_stats: C=%d must be a multiple of 8 and <= 2048", C);
+    CS_REQUIRE(acc && ticket && mean && rstd, "bn_stats_finalize: null workspace / output");
+    const int rpb = kRedThreads / (C / 8);
+    const size_t smem = (size_t)rpb * 2 * C * sizeof(float);
+    CS_REQUIRE(coef == nullptr || (gamma && beta), "bn_stats_finalize: coef needs gamma and beta");
+    BnStatsTail t{ticket, mean, rstd, rm, rv, (float)rows, eps, momentum, gamma, beta, coef};
+    bn_stats_kernel<<<red_grid(rows, rpb, 4), kRedThreads, smem, st>>>((const uint4*)x, acc, rows, C, t);
     CS_CUDA_OK(cudaGetLastError());
     return CS_OK;
 }
@@ -389,7 +569,25 @@ int bn_bwd_reduce(const void* x, const void* y, const void* dy, const float* mea
     const int rpb = kRedThreads / (C / 8);
     const size_t smem = (size_t)rpb * 2 * C * sizeof(float);
     bn_bwd_reduce_kernel<<<red_grid(rows, rpb, 2), kRedThreads, smem, st>>>((const uint4*)x, (const uint4*)y, (const uint4*)dy, mean,
-                                                                            rstd, dgamma, dbeta, rows, C, relu);
+                                                                            rstd, dgamma, dbeta, rows, C, relu, BnBwdTail{});
+    CS_CUDA_OK(cudaGetLastError());
+    return CS_OK;
+}
+
+// same reduction through the persistent workspace (`acc` [2C] + `ticket`, zero before the first call, left zero):
+// dgamma / dbeta need no zero fill, and with gamma_grad / beta_grad the parameter gradients are accumulated here too
+int bn_bwd_reduce_ws(const void* x, const void* y, const void* dy, const float* mean, const float* rstd, float* acc, int32_t* ticket,
+                     float* dgamma, float* dbeta, float* gamma_grad, float* beta_grad, const float* gamma, float* coef, int64_t rows,
+                     int C, int relu, cudaStream_t st) {
+    CS_REQUIRE(C >= 8 && C % 8 == 0 && C <= 2048, "bn_bwd: C=%d must be a multiple of 8 and <= 2048", C);
+    CS_REQUIRE(acc && ticket && dgamma && dbeta, "bn_bwd_reduce_ws: null workspace / output");
+    CS_REQUIRE((gamma_grad == nullptr) == (beta_grad == nullptr), "bn_bwd_reduce_ws: give both gradient pointers or neither");
+    const int rpb = kRedThreads / (C / 8);
+    const size_t smem = (size_t)rpb * 2 * C * sizeof(float);
+    CS_REQUIRE(coef == nullptr || gamma, "bn_bwd_reduce_ws: coef needs gamma");
+    BnBwdTail t{ticket, dgamma, dbeta, gamma_grad, beta_grad, gamma, coef, 1.0f / (float)rows};
+    bn_bwd_reduce_kernel<<<red_grid(rows, rpb, 2), kRedThreads, smem, st>>>((const uint4*)x, (const uint4*)y, (const uint4*)dy, mean,
+                                                                            rstd, acc, acc + C, rows, C, relu, t);
     CS_CUDA_OK(cudaGetLastError());
     return CS_OK;
 }

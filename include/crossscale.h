@@ -136,6 +136,12 @@ int cs_conv1d_dgrad(const void* dy, const void* wt, void* dx, int B, int L, int 
                     int K, int pad, int stride, cs_stream_t stream);
 int cs_conv1d_prepare_dgrad_weight(const void* w, void* wt, int K, int Cout, int Cin,
                                    cs_stream_t stream);
+/* Same dx, read straight from the FORWARD weights w [K, Cout, Cin] (the tile is used as an
+ * MN-major operand, taps in reverse): no transposed copy.  Covers Cin % 64 == 0 && Cout % 64 == 0
+ * with windows longer than 16 rows; returns CS_ERR_UNSUPPORTED (and launches nothing) otherwise —
+ * the caller then falls back to cs_conv1d_prepare_dgrad_weight + cs_conv1d_dgrad. */
+int cs_conv1d_dgrad_direct(const void* dy, const void* w, void* dx, int B, int L, int Cin,
+                           int Cout, int K, int pad, int stride, cs_stream_t stream);
 /* dw[K,Cout,Cin] (fp32, accumulated: caller zeroes) += sum_{b,l} dy[b,l,co]*x[b,l*s+k-pad,ci];
  * dbias[Cout] (fp32, optional) += sum dy. */
 int cs_conv1d_wgrad(const void* x, const void* dy, float* dw, float* dbias, int B, int L, int Cin,
@@ -170,6 +176,28 @@ int cs_bn_bwd_apply(const void* x, const void* y, const void* dy, const float* m
 int cs_bn_finalize(const float* stats, float* mean, float* rstd, float* running_mean,
                    float* running_var, int C, int64_t rows, float eps, float momentum,
                    cs_stream_t stream);
+/* One-launch variants built on a persistent workspace: `acc` [2*C] fp32 + `ticket` [1] int32, zero before the
+ * first call and left zero by every call (the last block to finish consumes the totals and clears them), so
+ * a layer needs no fill, finalize or gradient-add launches.  One workspace per layer and stream.
+ *   cs_bn_stats_finalize = cs_bn_stats + cs_bn_finalize; with gamma/beta/coef it also writes the forward
+ *                          coefficients coef[0:C] = rstd*gamma, coef[C:2C] = beta - mean*rstd*gamma
+ *   cs_bn_bwd_reduce_ws  = cs_bn_bwd_reduce into dgamma/dbeta (no zero fill needed); with gamma_grad /
+ *                          beta_grad the same sums are added into the parameter gradients; with gamma/coef
+ *                          it writes the backward coefficients [a | p | q] (3*C): dx = a*d + p*x + q
+ *   cs_bn_apply_coef     : y = relu?(x*coef[c] + coef[C+c] (+ residual))
+ *   cs_bn_bwd_apply_coef : d = dy masked by y > 0 (if relu); dres = d; dx = a*d + p*x + q */
+int cs_bn_stats_finalize(const void* x, float* acc, int32_t* ticket, float* mean, float* rstd,
+                         float* running_mean, float* running_var, int64_t rows, int C, float eps,
+                         float momentum, const float* gamma, const float* beta, float* coef,
+                         cs_stream_t stream);
+int cs_bn_bwd_reduce_ws(const void* x, const void* y, const void* dy, const float* mean,
+                        const float* rstd, float* acc, int32_t* ticket, float* dgamma, float* dbeta,
+                        float* gamma_grad, float* beta_grad, const float* gamma, float* coef,
+                        int64_t rows, int C, int relu, cs_stream_t stream);
+int cs_bn_apply_coef(const void* x, const void* residual, void* y, const float* coef, int64_t rows,
+                     int C, int relu, cs_stream_t stream);
+int cs_bn_bwd_apply_coef(const void* x, const void* y, const void* dy, const float* coef, void* dx,
+                         void* dres, int64_t rows, int C, int relu, cs_stream_t stream);
 /* y[b,j,c] = (x[b,2j,c] + x[b,2j+1,c]) / 2, j < L/2 (bf16 channels-last); backward spreads dy/2 */
 int cs_avgpool2_fwd(const void* x, void* y, int B, int L, int C, cs_stream_t stream);
 int cs_avgpool2_bwd(const void* dy, void* dx, int B, int L, int C, cs_stream_t stream);

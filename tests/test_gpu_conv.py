@@ -103,6 +103,32 @@ def test_bn_relu_residual_kernels(relu, with_res, C):
     assert _rel(bn.running_mean, ref_bn.running_mean) < 1e-2 and _rel(bn.running_var, ref_bn.running_var) < 1e-2
 
 
+def test_bn_workspace_is_self_cleaning_and_grads_can_go_straight_to_the_arena():
+    """two steps through the same layer: the persistent accumulators / tickets are zero again after every kernel, the
+    second step matches the first, and with ``fused_grad`` the reduction kernel adds dgamma / dbeta into .grad itself"""
+    from crossscale.ops.norm_act import BNReLU1d
+    torch.manual_seed(5)
+    B, L, C = 6, 200, 128
+    x = _bf(torch.randn(B, L, C, device=DEV)).to(torch.bfloat16)
+    dy = _bf(torch.randn(B, L, C, device=DEV)).to(torch.bfloat16)
+    bn = BNReLU1d(C, relu=True).to(DEV)
+    grads = []
+    for fused in (False, True, True):
+        bn.fused_grad = fused
+        bn.weight.grad = torch.zeros(C, device=DEV) if fused else None
+        bn.bias.grad = torch.zeros(C, device=DEV) if fused else None
+        xi = x.clone().requires_grad_(True)
+        bn(xi).backward(dy)
+        torch.cuda.synchronize()
+        acc, ticket = bn._ws
+        assert float(acc.abs().max()) == 0.0 and int(ticket.abs().max()) == 0
+        grads.append((xi.grad.float().clone(), bn.weight.grad.clone(), bn.bias.grad.clone()))
+    for a, b in zip(grads[0], grads[1]):
+        assert _rel(a, b) < 1e-5
+    for a, b in zip(grads[1], grads[2]):
+        assert _rel(a, b) < 1e-5
+
+
 def test_pool_and_layout_kernels():
     from crossscale.ops import _lib
     from crossscale.ops.norm_act import global_avg_pool1d
