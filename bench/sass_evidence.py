@@ -9,7 +9,8 @@ REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(REPO, "lib", "libcrossscale_cuda.so")
 OUT = os.path.join(REPO, "profiles", "sass")
 KERNELS = ["tiny_umma_kernelILi4ELb0ELi2E", "tiny_umma_kernelILi4ELb1ELi2E", "tiny_ecg_f32_kernelILi2E", "conv1d_fwd_kernel",
-           "conv1d_wgrad_kernel", "fedavg_oneshot_kernelILb0E", "fedavg_twoshot_kernelILb0E", "fedavg_twoshot_kernelILb1E",
+           "conv1d_wgrad_kernel", "conv1d_fwd_sw128_kernel", "conv1d_wgrad_sw128_kernel", "bn_apply_coef_kernel",
+           "bn_bwd_apply_coef_kernel", "fedavg_oneshot_kernelILb0E", "fedavg_twoshot_kernelILb0E", "fedavg_twoshot_kernelILb1E",
            "fedavg_inplace_kernel", "fedavg_nvls_kernel", "barrier_kernel", "bn_stats_kernel", "bn_bwd_reduce_kernel",
            "sgd_momentum_kernel", "gather_rows_kernel", "ce_fwd_bwd_kernel", "cin1_fwd_kernel", "cin1_wgrad_kernel"]
 MN = re.compile(r"^\s+/\*[0-9a-f]{4,5}\*/\s+(?:@!?U?P\d+\s+)?([A-Za-z0-9_.]+)")
@@ -19,7 +20,7 @@ HEAD = """# SASS evidence (`cuobjdump -sass lib/libcrossscale_cuda.so`, sm_100a)
 
 Histogram of the tensor-core / TMA / TMEM / NVLink-relevant mnemonics per kernel.
 `UTCHMMA` = tcgen05.mma kind::f16, `LDTM` = tcgen05.ld, `UTCBAR` = tcgen05.commit, `UTCATOMSWS` = tcgen05.alloc/dealloc,
-`UTMALDG.4D` = cp.async.bulk.tensor.4d (TMA), `SYNCS.*` = mbarrier, `REDG.E.ADD.F32x4` = red.global.add.v4.f32,
+`UTMALDG.4D` / `UTMALDG.3D` = cp.async.bulk.tensor (TMA load), `UTMASTG.3D` = TMA store, `SYNCS.*` = mbarrier, `REDG.E.ADD.F32x4` = red.global.add.v4.f32,
 `STG/LDG.E.STRONG.SYS` + `MEMBAR.*.SYS` = the st.release.sys / ld.acquire.sys flag protocol of the cross-GPU barrier
 (the data loads/stores on peer-mapped pointers are ordinary `LDG`/`STG`: the address aperture routes them over NVLink);
 `LDGMC.E.ADD.F32x4...SYS` = multimem.ld_reduce (NVSwitch in-fabric reduction), the matching multimem.st shows as a `.SYS` store.
@@ -28,6 +29,9 @@ Histogram of the tensor-core / TMA / TMEM / NVLink-relevant mnemonics per kernel
 
 def main():
     os.makedirs(OUT, exist_ok=True)
+    for old in os.listdir(OUT):                            # stale excerpts of kernels that changed signature
+        if old.endswith(".sass.txt"):
+            os.remove(os.path.join(OUT, old))
     sass = subprocess.run(["cuobjdump", "-sass", LIB], capture_output=True, text=True).stdout
     md = [HEAD]
     for f in re.split(r"\n\s*Function : ", sass)[1:]:
@@ -42,7 +46,7 @@ def main():
         if pick:
             lo = max(0, pick[0] - 12)
             ex = [l[:130].rstrip() for l in lines[lo:lo + 70] if re.search(r"/\*[0-9a-f]{4,5}\*/\s+\S", l)]
-            short = re.sub(r"[^A-Za-z0-9]+", "_", name)[:60]
+            short = re.sub(r"[^A-Za-z0-9]+", "_", name)[:72]
             with open(os.path.join(OUT, short + ".sass.txt"), "w") as fh:
                 fh.write(f"// excerpt of {name} around its first tensor-core / TMA / system-scope instruction\n" + "\n".join(ex) + "\n")
     with open(os.path.join(OUT, "README.md"), "w") as fh:

@@ -3,6 +3,7 @@
 // pooling (K4) and layout converters.  All are CUDA-core kernels sized against HBM bandwidth:
 // 128-bit accesses, grid-stride loops, one pass over the data where the math allows it.
 #include "common/cs_common.cuh"
+#include <stdlib.h>
 
 namespace cs {
 
@@ -297,18 +298,22 @@ __global__ void __launch_bounds__(kRedThreads) bn_stats_kernel(const uint4* __re
     column_reduce_finish<2>(acc, out, C, g, rl, rpb, sm_red);
     if (t.ticket == nullptr || !last_block_arrives(t.ticket)) return;
     for (int c = threadIdx.x; c < C; c += blockDim.x) {
-        const float m = __ldcg(stats + c) / t.rows;
-        const float var = fmaxf(__ldcg(stats + C + c) / t.rows - m * m, 0.0f);
+        // every load of the tail is issued before the first use: one L2 round trip, not four
+        const float s0 = __ldcg(stats + c), s1 = __ldcg(stats + C + c);
+        const float rm = t.running_mean ? t.running_mean[c] : 0.0f, rv = t.running_mean ? t.running_var[c] : 0.0f;
+        const float ga = t.coef ? t.gamma[c] : 0.0f, be = t.coef ? t.beta[c] : 0.0f;
+        const float m = s0 / t.rows;
+        const float var = fmaxf(s1 / t.rows - m * m, 0.0f);
+        const float rs = rsqrtf(var + t.eps);
         t.mean[c] = m;
-        t.rstd[c] = rsqrtf(var + t.eps);
+        t.rstd[c] = rs;
         if (t.running_mean) {
-            t.running_mean[c] += t.momentum * (m - t.running_mean[c]);
-            t.running_var[c] += t.momentum * (var * (t.rows / fmaxf(t.rows - 1.0f, 1.0f)) - t.running_var[c]);
+            t.running_mean[c] = rm + t.momentum * (m - rm);
+            t.running_var[c] = rv + t.momentum * (var * (t.rows / fmaxf(t.rows - 1.0f, 1.0f)) - rv);
         }
         if (t.coef) {
-            const float sc = rsqrtf(var + t.eps) * t.gamma[c];
-            t.coef[c] = sc;
-            t.coef[C + c] = t.beta[c] - m * sc;
+            t.coef[c] = rs * ga;
+            t.coef[C + c] = be - m * rs * ga;
         }
         stats[c] = 0.0f; stats[C + c] = 0.0f;
     }
@@ -376,15 +381,17 @@ __global__ void __launch_bounds__(kRedThreads) bn_bwd_reduce_kernel(const uint4*
     if (t.ticket == nullptr || !last_block_arrives(t.ticket)) return;
     for (int c = threadIdx.x; c < C; c += blockDim.x) {      // here dgamma / dbeta are the persistent accumulators
         const float dg = __ldcg(dgamma + c), db = __ldcg(dbeta + c);
+        const float gg = t.gamma_grad ? t.gamma_grad[c] : 0.0f, bg = t.gamma_grad ? t.beta_grad[c] : 0.0f;
+        const float ga = t.coef ? t.gamma[c] : 0.0f, rs = rstd[c], mu = mean[c];
         t.dgamma[c] = dg; t.dbeta[c] = db;
-        if (t.gamma_grad) { t.gamma_grad[c] += dg; t.beta_grad[c] += db; }
+        if (t.gamma_grad) { t.gamma_grad[c] = gg + dg; t.beta_grad[c] = bg + db; }
         if (t.coef) {
             // dx = gamma*rstd*(d - (dbeta + xhat*dgamma)/n), xhat = (x - mean)*rstd   ->   a*d + p*x + q
-            const float a = t.gamma[c] * rstd[c];
-            const float pc = -a * t.inv_rows * dg * rstd[c];
+            const float a = ga * rs;
+            const float pc = -a * t.inv_rows * dg * rs;
             t.coef[c] = a;
             t.coef[C + c] = pc;
-            t.coef[2 * C + c] = -a * t.inv_rows * db - pc * mean[c];
+            t.coef[2 * C + c] = -a * t.inv_rows * db - pc * mu;
         }
         dgamma[c] = 0.0f; dbeta[c] = 0.0f;
     }
@@ -518,9 +525,15 @@ int bn_bwd_apply_coef(const void* x, const void* y, const void* dy, const float*
     return CS_OK;
 }
 
+static int env_red_ctas_per_sm() {
+    static int v = 0;
+    if (!v) { const char* e = getenv("CS_BN_RED_CTAS"); v = (e && *e) ? atoi(e) : 2; if (v < 1) v = 1; if (v > 8) v = 8; }
+    return v;
+}
+
 static int red_grid(int64_t rows, int rpb, int unroll) {
-    int64_t want = (rows + (int64_t)rpb * unroll * 4 - 1) / ((int64_t)rpb * unroll * 4);   // >= 4 passes per thread
-    const int64_t cap = num_sms();
+    int64_t want = (rows + (int64_t)rpb * unroll * 2 - 1) / ((int64_t)rpb * unroll * 2);   // >= 2 passes per thread
+    const int64_t cap = (int64_t)num_sms() * env_red_ctas_per_sm();
     if (want > cap) want = cap;
     return (int)(want < 1 ? 1 : want);
 }
