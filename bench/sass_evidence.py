@@ -9,7 +9,7 @@ REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(REPO, "lib", "libcrossscale_cuda.so")
 OUT = os.path.join(REPO, "profiles", "sass")
 KERNELS = ["tiny_umma_kernelILi4ELb0ELi2E", "tiny_umma_kernelILi4ELb1ELi2E", "tiny_ecg_f32_kernelILi2E", "conv1d_fwd_kernel",
-           "conv1d_wgrad_kernel", "conv1d_fwd_sw128_kernel", "conv1d_wgrad_sw128_kernel", "bn_apply_coef_kernel",
+           "conv1d_wgrad_kernel", "conv1d_fwd_sw128_kernel", "conv1d_fwd_pair_kernel", "conv1d_wgrad_sw128_kernel", "bn_apply_coef_kernel",
            "bn_bwd_apply_coef_kernel", "fedavg_oneshot_kernelILb0E", "fedavg_twoshot_kernelILb0E", "fedavg_twoshot_kernelILb1E",
            "fedavg_inplace_kernel", "fedavg_nvls_kernel", "barrier_kernel", "bn_stats_kernel", "bn_bwd_reduce_kernel",
            "sgd_momentum_kernel", "gather_rows_kernel", "ce_fwd_bwd_kernel", "cin1_fwd_kernel", "cin1_wgrad_kernel"]

@@ -329,14 +329,23 @@ static int make_row_map(CUtensorMap* m, const void* base, int outer, int rows, i
 // Sized so that TWO CTAs fit one SM (<= 113 KB shared, <= 256 TMEM columns each): while one CTA drains its
 // accumulators and ramps up its first loads the other keeps the tensor core busy (measured 1.16 -> 1.36
 // PFLOP/s at C = 256, K = 7 against one 4-tile CTA per SM).
-__global__ void __launch_bounds__(kFwdThreads, 1)
-conv1d_fwd_sw128_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_w,
-                        const __grid_constant__ CUtensorMap map_y, const __grid_constant__ CUtensorMap map_xs,
-                        const float* __restrict__ bias, __nv_bfloat16* __restrict__ y, Fwd128Shape s) {
+// PAIR = true: the CTA is one half of a cta_group::2 pair (cluster of two along grid.x).  The pair issues ONE
+// M256 x N(NT) x K16 MMA per step: each CTA stages its own position tiles (A rows) and its own NT/2 rows of the
+// weight tile, so per MMA a CTA reads half the B bytes from shared memory (the single-CTA M128 x N128 shape sits on
+// the 128 B/clk shared-memory port) and streams half the weights from L2.  Only the leader (cluster rank 0) waits on
+// the "full" barriers and issues MMAs; both CTAs load, and both drain their own 128 accumulator lanes.
+template <bool PAIR>
+__device__ __forceinline__ void conv1d_fwd_sw128_body(const CUtensorMap& map_x, const CUtensorMap& map_w, const CUtensorMap& map_y,
+                                                      const CUtensorMap& map_xs, const float* __restrict__ bias,
+                                                      __nv_bfloat16* __restrict__ y, const Fwd128Shape& s) {
     extern __shared__ uint8_t smem_raw[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int n0 = blockIdx.x * s.NT, t0 = (blockIdx.z * gridDim.y + blockIdx.y) * s.MT;
-    if (t0 >= s.total) return;                               // padding CTAs of the (y, z) split
+    const uint32_t rank = PAIR ? cluster_ctarank() : 0u;
+    // single CTAs: grid = (cout tile, unit y, unit z).  Pairs: grid = (unit, cout tile) — the two CTAs of a
+    // cta_group::2 pair must be neighbours along x (a cluster with an odd x extent is rejected at launch)
+    const int n0 = (PAIR ? blockIdx.y : blockIdx.x) * s.NT;
+    const int t0 = (PAIR ? blockIdx.x : blockIdx.z * gridDim.y + blockIdx.y) * s.MT;
+    if (t0 - (int)rank * s.MT >= s.total) return;            // padding CTAs of the unit split (pair-uniform)
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw);
     uint64_t* full_a = bars, *empty_a = bars + 2, *full_w = bars + 4, *empty_w = full_w + kMaxWStages;
     uint64_t* acc_full = empty_w + kMaxWStages;
@@ -344,7 +353,8 @@ conv1d_fwd_sw128_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_
     // operand rings start on a 1024-byte boundary of the shared window (the swizzle pattern is address based)
     uint8_t* a_ring = smem_raw + (((smem_u32(smem_raw) + 256 + 1023) & ~1023u) - smem_u32(smem_raw));
     const int a_bytes = s.tile_stride * s.MT;
-    const int w_bytes = s.NT * 128;
+    const int w_rows = PAIR ? s.NT / 2 : s.NT;               // weight rows (output channels) this CTA stages
+    const int w_bytes = w_rows * 128;
     uint8_t* w_ring = a_ring + s.AS * a_bytes;
     const int chunks = s.Cin / 64;
     uint32_t tmem_cols = 32;
@@ -357,11 +367,22 @@ conv1d_fwd_sw128_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_
         fence_mbar_init();
         tma_prefetch_desc(&map_x); tma_prefetch_desc(&map_w); tma_prefetch_desc(&map_y); tma_prefetch_desc(&map_xs);
     }
-    if (warp == 1) tmem_alloc(tmem_slot, tmem_cols);
+    if (PAIR) {
+        cluster_sync();                                      // the peer's barriers exist before anything can arrive on them
+        if (warp == 1) tmem_alloc_pair(tmem_slot, tmem_cols);
+    } else if (warp == 1) {
+        tmem_alloc(tmem_slot, tmem_cols);
+    }
     tc_fence_before_sync();
     __syncthreads();
     tc_fence_after_sync();
     const uint32_t tmem_base = *tmem_slot;
+    // loads of both CTAs are counted on the LEADER's full barriers
+    const uint32_t txm = PAIR ? 2u : 1u;
+    auto load3 = [&](void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1, int c2) {
+        if (PAIR) tma_load_3d_pair(dst, map, mapa_shared(smem_u32(bar), 0), c0, c1, c2);
+        else tma_load_3d(dst, map, bar, c0, c1, c2);
+    };
 
     if (warp == 0) {
         // ===== TMA producer =====
@@ -371,39 +392,41 @@ conv1d_fwd_sw128_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_
                 const int sa = c % s.AS;
                 if (c >= s.AS) mbar_wait(empty_a + sa, ((c / s.AS) - 1) & 1);
                 if (!s.slot) {
-                    mbar_arrive_expect_tx(full_a + sa, s.R * 128 * s.MT);
+                    if (rank == 0) mbar_arrive_expect_tx(full_a + sa, txm * s.R * 128 * s.MT);
                     for (int i = 0; i < s.MT; ++i) {
                         // tiles past the end of the list are fetched out of bounds (sample index >= B): zero fill
                         const int t = t0 + i, tb = t / s.tiles, tl = (t % s.tiles) * 128;
-                        tma_load_3d(a_ring + sa * a_bytes + i * s.tile_stride, &map_x, full_a + sa, c * 64, tl - s.pad, tb);
+                        load3(a_ring + sa * a_bytes + i * s.tile_stride, &map_x, full_a + sa, c * 64, tl - s.pad, tb);
                     }
                 } else {
                     // one `slot`-row box per sample; rows 128 .. R-1 of the tile are never written and only feed outputs
                     // that the epilogue drops (l >= Lout of the last sample)
                     const int spt = 128 / s.slot;
-                    mbar_arrive_expect_tx(full_a + sa, 128 * 128 * s.MT);
+                    if (rank == 0) mbar_arrive_expect_tx(full_a + sa, txm * 128 * 128 * s.MT);
                     for (int i = 0; i < s.MT; ++i)
                         for (int j = 0; j < spt; ++j)
-                            tma_load_3d(a_ring + sa * a_bytes + i * s.tile_stride + j * s.slot * 128, &map_xs, full_a + sa, c * 64,
-                                        -s.pad, (t0 + i) * spt + j);
+                            load3(a_ring + sa * a_bytes + i * s.tile_stride + j * s.slot * 128, &map_xs, full_a + sa, c * 64,
+                                  -s.pad, (t0 + i) * spt + j);
                 }
                 for (int k = 0; k < s.K; ++k, ++wi) {
                     const int sw = wi % s.WS;
                     if (wi >= s.WS) mbar_wait(empty_w + sw, ((wi / s.WS) - 1) & 1);
-                    mbar_arrive_expect_tx(full_w + sw, w_bytes);
+                    if (rank == 0) mbar_arrive_expect_tx(full_w + sw, txm * w_bytes);
+                    const int nw = n0 + (int)rank * w_rows;     // this CTA's slice of the output channels
                     if (!s.wmn) {
-                        tma_load_3d(w_ring + sw * w_bytes, &map_w, full_w + sw, c * 64, n0, k);
+                        load3(w_ring + sw * w_bytes, &map_w, full_w + sw, c * 64, nw, k);
                     } else {
-                        for (int h = 0; h < s.NT / 64; ++h)     // 64 reduction rows x 64 output channels per box
-                            tma_load_3d(w_ring + sw * w_bytes + h * 8192, &map_w, full_w + sw, n0 + h * 64, c * 64, s.K - 1 - k);
+                        for (int h = 0; h < w_rows / 64; ++h)   // 64 reduction rows x 64 output channels per box
+                            load3(w_ring + sw * w_bytes + h * 8192, &map_w, full_w + sw, nw + h * 64, c * 64, s.K - 1 - k);
                     }
                 }
             }
         }
     } else if (warp == 1) {
-        // ===== MMA issuer =====
-        if (elect_one()) {
-            const uint32_t idesc = idesc_f16(FMT_BF16, 128, s.NT, MAJOR_K, s.wmn ? MAJOR_MN : MAJOR_K);
+        // ===== MMA issuer (pair: the leader only) =====
+        if (rank == 0 && elect_one()) {
+            const uint32_t idesc = idesc_f16(FMT_BF16, PAIR ? 256 : 128, s.NT, MAJOR_K, s.wmn ? MAJOR_MN : MAJOR_K);
+            auto commit = [&](uint64_t* bar) { if (PAIR) mma_commit_pair(bar); else mma_commit(bar); };
             int wi = 0;
             uint32_t first = 1;
             for (int c = 0; c < chunks; ++c) {
@@ -425,15 +448,16 @@ conv1d_fwd_sw128_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_
                         for (int i = 0; i < s.MT; ++i) {
                             // tap k = k rows (k * 128 B) further down the tile; 16-channel step = 32 B inside the row
                             const uint64_t a = smem_desc_sw128(a_addr + i * s.tile_stride + k * 128 + j * 32, 1024);
-                            mma_f16(tmem_base + i * s.NT, a, bd, idesc, (first && j == 0) ? 0u : 1u);
+                            if (PAIR) mma_f16_pair(tmem_base + i * s.NT, a, bd, idesc, (first && j == 0) ? 0u : 1u);
+                            else mma_f16(tmem_base + i * s.NT, a, bd, idesc, (first && j == 0) ? 0u : 1u);
                         }
                     }
                     first = 0;
-                    mma_commit(empty_w + sw);
+                    commit(empty_w + sw);
                 }
-                mma_commit(empty_a + sa);
+                commit(empty_a + sa);
             }
-            mma_commit(acc_full);
+            commit(acc_full);
         }
     } else {
         // ===== epilogue: TMEM -> registers -> bias/ReLU -> bf16 -> (swizzled slab -> TMA store | global) =====
@@ -514,8 +538,27 @@ conv1d_fwd_sw128_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_
         }
     }
     tc_fence_before_sync();
-    __syncthreads();
-    if (warp == 1) tmem_dealloc(tmem_base, tmem_cols);
+    if (PAIR) {
+        cluster_sync();                                      // both CTAs are done with both shared memories and TMEMs
+        if (warp == 1) tmem_dealloc_pair(tmem_base, tmem_cols);
+    } else {
+        __syncthreads();
+        if (warp == 1) tmem_dealloc(tmem_base, tmem_cols);
+    }
+}
+
+__global__ void __launch_bounds__(kFwdThreads, 1)
+conv1d_fwd_sw128_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_w,
+                        const __grid_constant__ CUtensorMap map_y, const __grid_constant__ CUtensorMap map_xs,
+                        const float* __restrict__ bias, __nv_bfloat16* __restrict__ y, const Fwd128Shape s) {
+    conv1d_fwd_sw128_body<false>(map_x, map_w, map_y, map_xs, bias, y, s);
+}
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kFwdThreads, 1)
+conv1d_fwd_pair_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_w,
+                       const __grid_constant__ CUtensorMap map_y, const __grid_constant__ CUtensorMap map_xs,
+                       const float* __restrict__ bias, __nv_bfloat16* __restrict__ y, const Fwd128Shape s) {
+    conv1d_fwd_sw128_body<true>(map_x, map_w, map_y, map_xs, bias, y, s);
 }
 
 static int env_int(const char* name, int dflt) {
@@ -524,7 +567,8 @@ static int env_int(const char* name, int dflt) {
 }
 
 // Launches the 128-byte-row variant and returns CS_OK (or an error), or -1 when the shape is not one it covers.
-// Tuning overrides for experiments: CS_CONV_SW128=0 (use the plane kernel), CS_CONV_MT / CS_CONV_AS / CS_CONV_WS.
+// Tuning overrides for experiments: CS_CONV_SW128=0 (use the plane kernel), CS_CONV_PAIR=0 (no cta_group::2 pairs),
+// CS_CONV_MT / CS_CONV_AS / CS_CONV_WS.
 static int conv1d_fwd_sw128(const void* x, const void* w, const float* bias, void* y, int B, int L, int Cin, int Cout, int K,
                             int pad, int relu, int Lout, cudaStream_t st, int wmn) {
     if (Cin % 64 != 0 || Cout % 32 != 0 || Lout + K - 1 <= 16 || !env_int("CS_CONV_SW128", 1)) return -1;
@@ -532,7 +576,6 @@ static int conv1d_fwd_sw128(const void* x, const void* w, const float* bias, voi
     Fwd128Shape s;
     s.wmn = wmn;
     s.B = B; s.L = L; s.Lout = Lout; s.Cin = Cin; s.Cout = Cout; s.K = K; s.pad = pad; s.relu = relu;
-    s.NT = Cout % 128 == 0 ? 128 : (Cout % 64 == 0 ? 64 : 32);
     s.R = 128 + K - 1;
     s.tile_stride = (s.R * 128 + 1023) & ~1023;
     s.tiles = (Lout + 127) / 128;
@@ -543,34 +586,57 @@ static int conv1d_fwd_sw128(const void* x, const void* w, const float* bias, voi
         s.tiles = 1;
         s.total = (B + 128 / s.slot - 1) / (128 / s.slot);
     }
-    auto need = [&]() { return (size_t)2048 + (size_t)s.AS * s.tile_stride * s.MT + (size_t)s.WS * s.NT * 128; };
-    // preferred: two co-resident CTAs per SM (256 TMEM columns and <= 113 KB shared memory each)
     const size_t kHalfSm = 113 * 1024, kFullSm = 227 * 1024;
-    s.MT = 256 / s.NT; if (s.MT > 4) s.MT = 4; if (s.MT > s.total) s.MT = s.total;
-    // small problems: fewer tiles per CTA so that every SM gets work (weights are re-streamed from L2, which is cheap here)
-    while (s.MT > 1 && (long long)(Cout / s.NT) * ((s.total + s.MT - 1) / s.MT) < 2LL * num_sms()) s.MT >>= 1;
-    s.AS = 2; s.WS = 4;
-    while (need() > kHalfSm && s.WS > 2) --s.WS;
-    if (need() > kHalfSm) {                                  // wide taps: one activation stage, the sibling CTA covers the bubble
-        s.AS = 1; s.WS = 4;
-        while (need() > kHalfSm && s.WS > 2) --s.WS;
+    int pair = 0;
+    auto need = [&]() {
+        return (size_t)2048 + (size_t)s.AS * s.tile_stride * s.MT + (size_t)s.WS * (pair ? s.NT / 2 : s.NT) * 128;
+    };
+    // --- CTA pairs: N up to 256 per MMA, each CTA stages half of the weight tile.  Worth it once there are enough
+    //     tiles to fill the machine with pairs; (wmn needs whole 64-channel blocks per CTA)
+    {
+        const int nt = Cout % 256 == 0 ? 256 : (Cout % 128 == 0 ? 128 : (Cout % 64 == 0 ? 64 : 0));
+        if (nt && (!wmn || nt >= 128) && env_int("CS_CONV_PAIR", 1)) {
+            s.NT = nt; s.MT = 256 / nt; s.AS = 2; s.WS = 4;
+            pair = 1;
+            while (need() > kHalfSm && s.WS > 2) --s.WS;
+            if (need() > kHalfSm) { s.AS = 1; s.WS = 4; while (need() > kHalfSm && s.WS > 2) --s.WS; }
+            // measured: pairs win 5-8 % with N = 256 per MMA (1.40 vs 1.33 PFLOP/s at C=256 K=7, 1.52 vs 1.40 at K=31) and
+            // lose a little with N = 128 / 64 or when there are too few tiles to keep every TPC busy with pairs
+            const long long ctas = (long long)(Cout / nt) * ((s.total + s.MT - 1) / s.MT);
+            if (need() > kHalfSm || ctas < 4LL * num_sms() || nt != 256) pair = 0;
+            if (env_int("CS_CONV_PAIR", 1) == 2 && need() <= kFullSm) pair = 1;      // forced (tests)
+        }
     }
-    if (need() > kHalfSm) {                                  // very wide taps: one CTA per SM, all of TMEM
+    if (!pair) {
+        s.NT = Cout % 128 == 0 ? 128 : (Cout % 64 == 0 ? 64 : 32);
+        // preferred: two co-resident CTAs per SM (256 TMEM columns and <= 113 KB shared memory each)
+        s.MT = 256 / s.NT; if (s.MT > 4) s.MT = 4; if (s.MT > s.total) s.MT = s.total;
+        // small problems: fewer tiles per CTA so that every SM gets work (weights are re-streamed from L2, which is cheap here)
+        while (s.MT > 1 && (long long)(Cout / s.NT) * ((s.total + s.MT - 1) / s.MT) < 2LL * num_sms()) s.MT >>= 1;
         s.AS = 2; s.WS = 4;
-        s.MT = 512 / s.NT; if (s.MT > 4) s.MT = 4; if (s.MT > s.total) s.MT = s.total;
-        while (need() > kFullSm && s.MT > 1) s.MT >>= 1;
-        while (need() > kFullSm && s.WS > 2) --s.WS;
-        if (need() > kFullSm) return -1;
+        while (need() > kHalfSm && s.WS > 2) --s.WS;
+        if (need() > kHalfSm) {                              // wide taps: one activation stage, the sibling CTA covers the bubble
+            s.AS = 1; s.WS = 4;
+            while (need() > kHalfSm && s.WS > 2) --s.WS;
+        }
+        if (need() > kHalfSm) {                              // very wide taps: one CTA per SM, all of TMEM
+            s.AS = 2; s.WS = 4;
+            s.MT = 512 / s.NT; if (s.MT > 4) s.MT = 4; if (s.MT > s.total) s.MT = s.total;
+            while (need() > kFullSm && s.MT > 1) s.MT >>= 1;
+            while (need() > kFullSm && s.WS > 2) --s.WS;
+            if (need() > kFullSm) return -1;
+        }
+        { const int v = env_int("CS_CONV_MT", 0); if (v > 0 && v * s.NT <= 512) s.MT = v; }
     }
-    { const int v = env_int("CS_CONV_MT", 0); if (v > 0 && v * s.NT <= 512) s.MT = v; }
     { const int v = env_int("CS_CONV_AS", 0); if (v == 1 || v == 2) s.AS = v; }
     { const int v = env_int("CS_CONV_WS", 0); if (v >= 2 && v <= kMaxWStages) s.WS = v; }
     if (need() > kFullSm) return -1;
-    s.tma_store = (s.NT % 64 == 0 && (size_t)s.AS * s.tile_stride * s.MT >= 32768) ? 1 : 0;
+    s.tma_store = (s.NT % 64 == 0 && (size_t)s.AS * s.tile_stride * s.MT >= 32768 && env_int("CS_CONV_TMA_STORE", 1)) ? 1 : 0;
+    const int w_rows = pair ? s.NT / 2 : s.NT;
     CUtensorMap mx, mw;
     int rc = make_row_map(&mx, x, B, L, Cin, s.R);
     if (rc) return rc;
-    rc = wmn ? make_row_map(&mw, w, K, Cin, Cout, 64) : make_row_map(&mw, w, K, Cout, Cin, s.NT);
+    rc = wmn ? make_row_map(&mw, w, K, Cin, Cout, 64) : make_row_map(&mw, w, K, Cout, Cin, w_rows);
     if (rc) return rc;
     CUtensorMap my = mw, mxs = mx;
     if (s.tma_store) {
@@ -582,16 +648,42 @@ static int conv1d_fwd_sw128(const void* x, const void* w, const float* bias, voi
         if (rc) return rc;
     }
     const size_t smem = need();
-    static size_t configured[64] = {};
+    static size_t configured[2][64] = {};
     int dev = 0;
     CS_CUDA_OK(cudaGetDevice(&dev));
-    if (smem > configured[dev & 63]) {
-        CS_CUDA_OK(cudaFuncSetAttribute(conv1d_fwd_sw128_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured[dev & 63] = smem;
+    if (smem > configured[pair][dev & 63]) {
+        if (pair) CS_CUDA_OK(cudaFuncSetAttribute(conv1d_fwd_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        else CS_CUDA_OK(cudaFuncSetAttribute(conv1d_fwd_sw128_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        // ask for the largest shared-memory carve-out: two ~104 KB CTAs only fit one SM with the full 228 KB
+        if (env_int("CS_CONV_CARVEOUT", 1)) {
+            if (pair) CS_CUDA_OK(cudaFuncSetAttribute(conv1d_fwd_pair_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+            else CS_CUDA_OK(cudaFuncSetAttribute(conv1d_fwd_sw128_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+        }
+        configured[pair][dev & 63] = smem;
     }
-    const int units = (s.total + s.MT - 1) / s.MT, gy = units < 32768 ? units : 32768;
+    int units = (s.total + s.MT - 1) / s.MT;
+    if (pair) units = (units + 1) & ~1;                      // whole pairs; the odd one out loads zeros and stores nothing
+    int gy = units < 32768 ? units : 32768;
     dim3 grid(Cout / s.NT, gy, (units + gy - 1) / gy);
-    conv1d_fwd_sw128_kernel<<<grid, kFwdThreads, smem, st>>>(mx, mw, my, mxs, bias, (__nv_bfloat16*)y, s);
+    if (pair) grid = dim3(units, Cout / s.NT, 1);
+    if (env_int("CS_CONV_DEBUG", 0)) {
+        int occ = -1;
+        if (pair) {
+            cudaLaunchConfig_t cfg = {};
+            cfg.gridDim = grid; cfg.blockDim = dim3(kFwdThreads); cfg.dynamicSmemBytes = smem;
+            cudaLaunchAttribute attr[1];
+            attr[0].id = cudaLaunchAttributeClusterDimension;
+            attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+            cfg.attrs = attr; cfg.numAttrs = 1;
+            cudaOccupancyMaxActiveClusters(&occ, conv1d_fwd_pair_kernel, &cfg);
+        } else {
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, conv1d_fwd_sw128_kernel, kFwdThreads, smem);
+        }
+        fprintf(stderr, "[conv sw128] pair=%d grid=(%u,%u,%u) smem=%zu NT=%d MT=%d AS=%d WS=%d occupancy(%s)=%d\n", pair, grid.x, grid.y,
+                grid.z, smem, s.NT, s.MT, s.AS, s.WS, pair ? "clusters on the device" : "CTAs per SM", occ);
+    }
+    if (!pair) conv1d_fwd_sw128_kernel<<<grid, kFwdThreads, smem, st>>>(mx, mw, my, mxs, bias, (__nv_bfloat16*)y, s);
+    else conv1d_fwd_pair_kernel<<<grid, kFwdThreads, smem, st>>>(mx, mw, my, mxs, bias, (__nv_bfloat16*)y, s);   // cluster (2,1,1)
     CS_CUDA_OK(cudaGetLastError());
     return CS_OK;
 }

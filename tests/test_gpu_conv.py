@@ -50,6 +50,34 @@ def test_conv1d_fwd_dgrad_wgrad(B, L, Cin, Cout, K, pad):
     assert _rel(m.bias.grad, br.grad) < 5e-3
 
 
+@pytest.mark.parametrize("B,L,Cin,Cout,K,pad", [(5, 300, 128, 256, 7, 3), (3, 200, 64, 128, 5, 2), (9, 45, 256, 512, 7, 3), (2, 130, 64, 64, 3, 1)])
+def test_conv1d_cta_pair_kernel_matches_single_cta(monkeypatch, B, L, Cin, Cout, K, pad):
+    """cta_group::2 path (two CTAs of a cluster issue one M256 MMA, each staging half of the weight tile) forced on
+    small shapes — odd tile counts, packed short windows, both weight layouts — against the single-CTA kernel and
+    the fp32 oracle"""
+    from crossscale.ops import _lib
+    lib, st = _lib.cuda_lib(), _lib.stream_ptr()
+    torch.manual_seed(K + B)
+    x = _bf(torch.randn(B, L, Cin, device=DEV)).to(torch.bfloat16)
+    w = _bf(torch.randn(K, Cout, Cin, device=DEV) * 0.1).to(torch.bfloat16)
+    bias = torch.randn(Cout, device=DEV)
+    Lout = L + 2 * pad - K + 1
+    dy = _bf(torch.randn(B, Lout, Cout, device=DEV)).to(torch.bfloat16)
+    out = {}
+    for mode in ("0", "2"):
+        monkeypatch.setenv("CS_CONV_PAIR", mode)
+        y = torch.zeros(B, Lout, Cout, dtype=torch.bfloat16, device=DEV)
+        dx = torch.zeros(B, L, Cin, dtype=torch.bfloat16, device=DEV)
+        _lib.check(lib.cs_conv1d_fwd(x.data_ptr(), w.data_ptr(), bias.data_ptr(), y.data_ptr(), B, L, Cin, Cout, K, pad, 1, 1, st))
+        _lib.check(lib.cs_conv1d_dgrad_direct(dy.data_ptr(), w.data_ptr(), dx.data_ptr(), B, L, Cin, Cout, K, pad, 1, st))
+        torch.cuda.synchronize()
+        out[mode] = (y.float(), dx.float())
+    yr = F.relu(F.conv1d(x.float().permute(0, 2, 1), w.float().permute(1, 2, 0), bias, padding=pad)).permute(0, 2, 1)
+    assert _rel(out["2"][0], yr) < 1e-2
+    assert torch.equal(out["0"][0], out["2"][0])            # same MMA order per output element: bit-identical
+    assert _rel(out["2"][1], out["0"][1]) < 1e-6
+
+
 def test_conv1d_relu_epilogue_and_cin1():
     from crossscale.ops import _lib
     from crossscale.ops.conv1d import Conv1dB200, conv1d_fwd_nlc
