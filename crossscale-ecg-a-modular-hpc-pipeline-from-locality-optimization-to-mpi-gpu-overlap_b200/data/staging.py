@@ -69,6 +69,7 @@ class H2DStager:
         for ev in self.free:
             ev.record()
         self.h2d_bytes = 0
+        self.trace = None                # set to a list to collect (start, end) timing events of every H2D block copy
 
     def stage(self, slot: int, hx: torch.Tensor, hy: torch.Tensor) -> None:
         """Enqueue pinned ``hx``/``hy`` -> device slot on the copy stream (after the slot was released)."""
@@ -76,8 +77,15 @@ class H2DStager:
         assert hx.dtype == self.xs[slot].dtype and hx.is_contiguous()
         cs.wait_event(self.free[slot])
         nbx, nby = hx.numel() * hx.element_size(), hy.numel() * 8
+        if self.trace is not None:
+            t0 = torch.cuda.Event(enable_timing=True)
+            t0.record(cs)
         _lib.check(lib.cs_stage_h2d(self.xs[slot].data_ptr(), hx.data_ptr(), nbx, cs.cuda_stream), "cs_stage_h2d")
         _lib.check(lib.cs_stage_h2d(self.ys[slot].data_ptr(), hy.data_ptr(), nby, cs.cuda_stream), "cs_stage_h2d")
+        if self.trace is not None:
+            t1 = torch.cuda.Event(enable_timing=True)
+            t1.record(cs)
+            self.trace.append((t0, t1))
         self.ready[slot].record(cs)
         self.h2d_bytes = nbx + nby
 

@@ -442,10 +442,17 @@ class FedAvgRunner:
         rows = self.local_steps * self.batch
         self._store, self._sampler = store, BlockSampler(store.n, rows, seed)
         self._stager = H2DStager(rows, store.l, store.x.dtype, self.device)
-        self._loss_host = torch.zeros(8, dtype=torch.float32, pin_memory=True)
-        self._loss_prev, self._last_loss, self._e2e_rounds = 0.0, 0.0, 0
-        self._loss_events = [torch.cuda.Event(), torch.cuda.Event()]
-        self._loss_seen = [None, None]
+        # loss read-back ring: round r writes slot r % 4; the host reads every round's loss, `e2e_depth` rounds late
+        self._loss_slots = 4
+        self.e2e_depth = 2
+        self._loss_host = torch.zeros(4 * self._loss_slots, dtype=torch.float32, pin_memory=True)
+        self._loss_prev, self._last_loss, self._e2e_rounds, self._e2e_collected = 0.0, 0.0, 0, 0
+        self._loss_events = [torch.cuda.Event() for _ in range(self._loss_slots)]
+        # the D2H copy itself runs on a side stream from a per-round device snapshot of the running loss sum, so the
+        # training stream never waits on the copy engine between rounds
+        self._loss_ring = torch.zeros(self._loss_slots, dtype=torch.float32, device=self.device)
+        self._loss_snap = [torch.cuda.Event() for _ in range(self._loss_slots)]
+        self._rb_stream = torch.cuda.Stream(device=self.device)
         self._graphs = [None, None]
         self._slot = 0
         self._lib = _lib
@@ -461,12 +468,19 @@ class FedAvgRunner:
 
         ``pipelined=False``: the host waits for THIS round's loss before returning.
         ``pipelined=True``: this round is enqueued (H2D of the next block, 50 fused steps, aggregation, D2H of the
-        loss) and the host then collects the PREVIOUS round's loss, so the next round can be enqueued while this one
-        runs; every round's loss is still read back, one round late — call :meth:`drain_e2e` for the last one."""
+        loss) and the host then collects the loss of the round ``e2e_depth`` (2) rounds back, so a host hiccup
+        shorter than a round or two never idles the GPU; every round's loss is still read back by the host, in
+        order — call :meth:`drain_e2e` for the tail."""
+        trace = getattr(self, "e2e_trace", None)        # optional diagnostics: list of per-round dicts (bench --trace-e2e)
+        if trace is not None:
+            h0 = time.perf_counter()
         slot = self._slot
         xb, yb = self._stager.acquire(slot)
         self._stage_next(slot ^ 1)                  # next block's H2D overlaps this round's compute
         tr = self.trainer
+        if trace is not None:
+            ev0, ev1, ev2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+            ev0.record()
         if not tr.use_graph:
             tr.run_round_staged(xb, yb)
         else:
@@ -483,31 +497,42 @@ class FedAvgRunner:
                 g.replay()
                 tr.launches += self.local_steps
         self._stager.release(slot)
+        if trace is not None:
+            ev1.record()
         self.agg.aggregate(self.flat, self.prev, self.weight, self.mom)
         st = torch.cuda.current_stream(self.device)
-        k = self._e2e_rounds & 1                       # two pinned loss slots / events: one in flight, one being read
-        self._lib.check(self._lib.cuda_lib().cs_stage_d2h(self._loss_host.data_ptr() + 16 * k, tr.state.fstate.data_ptr(),
-                                                          4, st.cuda_stream), "cs_stage_d2h")
-        self._loss_events[k].record(st)
+        if trace is not None:
+            ev2.record()
+            h1 = time.perf_counter()
+        k = self._e2e_rounds % self._loss_slots
+        self._loss_ring[k:k + 1].copy_(tr.state.fstate[tk.FS_LOSS_SUM:tk.FS_LOSS_SUM + 1])      # snapshot, in stream order
+        self._loss_snap[k].record(st)
+        self._rb_stream.wait_event(self._loss_snap[k])
+        self._lib.check(self._lib.cuda_lib().cs_stage_d2h(self._loss_host.data_ptr() + 16 * k, self._loss_ring.data_ptr() + 4 * k,
+                                                          4, self._rb_stream.cuda_stream), "cs_stage_d2h")
+        self._loss_events[k].record(self._rb_stream)
         self._e2e_rounds += 1
         self._slot ^= 1
-        if pipelined and self._e2e_rounds > 1:
-            return self._collect_loss(k ^ 1)           # previous round (already or almost done)
-        return self._collect_loss(k)
+        depth = min(self.e2e_depth, self._loss_slots - 1) if pipelined else 0
+        out = self._collect_losses(self._e2e_rounds - depth)
+        if trace is not None:
+            trace.append({"ev": (ev0, ev1, ev2), "host_enqueue_ms": (h1 - h0) * 1e3, "host_total_ms": (time.perf_counter() - h0) * 1e3})
+        return out
 
-    def _collect_loss(self, k: int) -> float:
-        self._loss_events[k].synchronize()
-        total = float(self._loss_host[4 * k])
-        if total == self._loss_seen[k]:                # this slot was already consumed
-            return self._last_loss
-        self._loss_seen[k] = total
-        self._last_loss = (total - self._loss_prev) / self.local_steps
-        self._loss_prev = total
+    def _collect_losses(self, upto: int) -> float:
+        """host-side read of the per-round losses, in order, for rounds < ``upto``"""
+        while self._e2e_collected < upto:
+            k = self._e2e_collected % self._loss_slots
+            self._loss_events[k].synchronize()
+            total = float(self._loss_host[4 * k])
+            self._last_loss = (total - self._loss_prev) / self.local_steps
+            self._loss_prev = total
+            self._e2e_collected += 1
         return self._last_loss
 
     def drain_e2e(self) -> float:
-        """Read the loss of the last enqueued round (pipelined mode)."""
-        return self._collect_loss((self._e2e_rounds - 1) & 1)
+        """Read the losses of the rounds still in flight (pipelined mode)."""
+        return self._collect_losses(self._e2e_rounds)
 
     def close(self):
         if getattr(self.agg, "inplace", False):          # parameters live in the arena: move them out before it is freed

@@ -50,6 +50,7 @@ def test_runner_e2e_staged_path(synth_shards):
         assert all(l == l and 0 < l < 2 for l in losses) and losses[-1] < losses[0]
         lag = [r.run_round_e2e(pipelined=True) for _ in range(4)] + [r.drain_e2e()]
         assert all(l == l and 0 <= l < 2 for l in lag) and r.trainer.state.steps_done() == 40
+        assert r._e2e_collected == r._e2e_rounds == 10                      # every round's loss reached the host
         assert r._stager.h2d_bytes == 200 * 500 * (4 if dt == torch.float32 else 2) + 200 * 8
         r.close()
 
