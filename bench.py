@@ -169,9 +169,13 @@ def run_ours(args):
             period = mean([a["ev"][0].elapsed_time(b["ev"][0]) for a, b in zip(tr_[:-1], tr_[1:])])
             gap = mean([a["ev"][2].elapsed_time(b["ev"][0]) for a, b in zip(tr_[:-1], tr_[1:])])
             copy_ms = mean([a.elapsed_time(b) for a, b in cp_])
-            print(f"[e2e trace rank {rank}] round period {period:.3f} ms = 50 steps {steps_ms:.3f} + aggregation {agg_ms_:.3f} + gap to next "
-                  f"round {gap:.3f}; H2D block copy {copy_ms:.3f} ms; host enqueue {mean([t['host_enqueue_ms'] for t in tr_]):.3f} ms, host total "
-                  f"{mean([t['host_total_ms'] for t in tr_]):.3f} ms per round", file=sys.stderr, flush=True)
+            row = {"rank": rank, "period_ms": round(period, 4), "steps_ms": round(steps_ms, 4), "agg_incl_barrier_wait_ms": round(agg_ms_, 4),
+                   "gap_ms": round(gap, 4), "h2d_copy_ms": round(copy_ms, 4),
+                   "host_enqueue_ms": round(mean([t["host_enqueue_ms"] for t in tr_]), 4),
+                   "host_total_ms": round(mean([t["host_total_ms"] for t in tr_]), 4)}
+            for r_ in sorted(launch.gather_rows([row]), key=lambda r: r["rank"]):
+                sys.stderr.write("[e2e trace] " + json.dumps(r_) + "\n")
+            sys.stderr.flush()
         e2e = {"value": samples / (e2e_ms / 1e3), "unit": "samples/s",
                "h2d_bytes_per_step": int(runner._stager.h2d_bytes), "d2h_bytes_per_step": int(runner.d2h_bytes),
                "ms_per_step": e2e_ms / K, "device_ms_per_step": e2e_dev_ms / K, "wall_ms_per_step": wall_ms / K, "stage_dtype": str(dt).replace("torch.", ""), "last_loss": last,
