@@ -13,7 +13,7 @@ import torch
 import torch.nn as nn
 
 from ..ops.conv1d import Conv1dB200
-from ..ops.norm_act import BNReLU1d, avg_pool2, global_avg_pool1d
+from ..ops.norm_act import BNReLU1d, avg_pool2, conv_bn, global_avg_pool1d
 
 
 class BasicBlock1D(nn.Module):
@@ -35,9 +35,9 @@ class BasicBlock1D(nn.Module):
     def forward(self, x):
         if self.pool:
             x = avg_pool2(x)
-        idn = x if self.down is None else self.down_bn(self.down(x))
-        y = self.bn1(self.conv1(x))
-        return self.bn2(self.conv2(y), residual=idn)
+        idn = x if self.down is None else conv_bn(self.down, self.down_bn, x)
+        y = conv_bn(self.conv1, self.bn1, x)
+        return conv_bn(self.conv2, self.bn2, y, residual=idn)
 
 
 class ResNet1DWide(nn.Module):

@@ -39,13 +39,31 @@ def conv1d_fwd_nlc(x, w_kcoci, bias, pad, relu=False):
 
 class _ConvNLC(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, weight, bias, pad, w_bf16, module):
+    def forward(ctx, x, weight, bias, pad, w_bf16, module, bn_req=None):
+        """``bn_req``: optional dict from ``norm_act.BNReLU1d.stats_request`` — the forward kernel then also produces the
+        training-mode BatchNorm statistics of its output (``bn_req["done"]`` tells the BN op whether it did)."""
         w = w_bf16 if w_bf16 is not None else weight.detach().to(torch.bfloat16)        # [K, Cout, Cin]
         xc = x.contiguous()
         ctx.save_for_backward(xc, w)
         ctx.meta = (pad, module)
         ctx.params = (weight, bias)
-        return conv1d_fwd_nlc(xc, w, None if bias is None else bias.detach().float().contiguous(), pad)
+        b32 = None if bias is None else bias.detach().float().contiguous()
+        if bn_req is not None:
+            bsz, l, cin = xc.shape
+            k, cout, _ = w.shape
+            y = torch.empty((bsz, l + 2 * pad - k + 1, cout), dtype=torch.bfloat16, device=xc.device)
+            r = bn_req
+            rc = _lib.cuda_lib().cs_conv1d_fwd_bn(
+                xc.data_ptr(), w.data_ptr(), _lib.ptr(b32), y.data_ptr(), bsz, l, cin, cout, k, pad, 1, 0,
+                r["acc"].data_ptr(), r["ticket"].data_ptr(), r["mean"].data_ptr(), r["rstd"].data_ptr(), _lib.ptr(r["rm"]),
+                _lib.ptr(r["rv"]), float(r["eps"]), float(r["momentum"]), r["gamma"].data_ptr(), r["beta"].data_ptr(),
+                r["coef"].data_ptr(), _lib.stream_ptr())
+            if rc == _lib.CS_OK:
+                r["done"] = True
+                return y
+            if rc != _lib.CS_ERR_UNSUPPORTED:
+                _lib.check(rc, "cs_conv1d_fwd_bn")
+        return conv1d_fwd_nlc(xc, w, b32, pad)
 
     @staticmethod
     def backward(ctx, dy):
@@ -74,12 +92,12 @@ class _ConvNLC(torch.autograd.Function):
                        "cs_conv1d_wgrad")
             # autograd still runs the parameter's post-accumulate-grad hooks (e.g. GradSync buckets) after this
             # node returns, even though no gradient tensor is handed back
-            return dx, None, None, None, None, None
+            return dx, None, None, None, None, None, None
         dw = torch.zeros((k, cout, cin), dtype=torch.float32, device=x.device)
         db = torch.zeros(cout, dtype=torch.float32, device=x.device) if bias is not None else None
         _lib.check(lib.cs_conv1d_wgrad(x.data_ptr(), dy.data_ptr(), dw.data_ptr(), _lib.ptr(db), b, l, cin, cout, k, pad, 1, st),
                    "cs_conv1d_wgrad")
-        return dx, dw, db, None, None, None
+        return dx, dw, db, None, None, None, None
 
 
 class _ConvCin1(torch.autograd.Function):
@@ -133,9 +151,9 @@ class Conv1dB200(nn.Module):
         """PyTorch-layout view ``[Cout, Cin, K]`` of the tap-major parameter."""
         return self.weight.permute(1, 2, 0)
 
-    def forward(self, x: torch.Tensor) -> torch.Tensor:
+    def forward(self, x: torch.Tensor, bn_req=None) -> torch.Tensor:
         if not x.is_cuda:
             return F.conv1d(x, self.weight_oik, self.bias, padding=self.padding)
         if self.cin == 1:
             return _ConvCin1.apply(x, self.weight, self.bias, self.padding)
-        return _ConvNLC.apply(x, self.weight, self.bias, self.padding, self.weight_bf16, self)
+        return _ConvNLC.apply(x, self.weight, self.bias, self.padding, self.weight_bf16, self, bn_req)

@@ -20,15 +20,20 @@ class _BNAct(torch.autograd.Function):
     2 launches forward and 2 backward per layer with no fill / finalize / add kernels."""
 
     @staticmethod
-    def forward(ctx, x, gamma, beta, residual, relu, eps, mean_in, var_in, running, momentum, ws, module):
+    def forward(ctx, x, gamma, beta, residual, relu, eps, mean_in, var_in, running, momentum, ws, module, stats=None):
         lib, st = _lib.cuda_lib(), _lib.stream_ptr()
         x = x.contiguous()
         b, l, c = x.shape
         rows = b * l
-        g32, b32 = gamma.detach().float().contiguous(), beta.detach().float().contiguous()
-        buf = torch.empty(4 * c, dtype=torch.float32, device=x.device)
-        mean, rstd, coef = buf[:c], buf[c:2 * c], buf[2 * c:]
-        if mean_in is None:                                # training: batch statistics + running update in one launch
+        if stats is not None:                              # produced by the convolution that wrote x (fused epilogue)
+            g32, mean, rstd, coef = stats["gamma"], stats["mean"], stats["rstd"], stats["coef"]
+        else:
+            g32, b32 = gamma.detach().float().contiguous(), beta.detach().float().contiguous()
+            buf = torch.empty(4 * c, dtype=torch.float32, device=x.device)
+            mean, rstd, coef = buf[:c], buf[c:2 * c], buf[2 * c:]
+        if stats is not None:
+            pass
+        elif mean_in is None:                              # training: batch statistics + running update in one launch
             rm, rv = running if running is not None else (None, None)
             acc, ticket = ws
             _lib.check(lib.cs_bn_stats_finalize(x.data_ptr(), acc.data_ptr(), ticket.data_ptr(), mean.data_ptr(), rstd.data_ptr(),
@@ -75,8 +80,8 @@ class _BNAct(torch.autograd.Function):
         _lib.check(lib.cs_bn_bwd_apply_coef(x.data_ptr(), y.data_ptr(), dy.data_ptr(), coef.data_ptr(), dx.data_ptr(),
                                             _lib.ptr(dres), rows, c, int(relu), st), "cs_bn_bwd_apply_coef")
         if fused:
-            return dx, None, None, dres, None, None, None, None, None, None, None, None
-        return dx, dgamma, dbeta, dres, None, None, None, None, None, None, None, None
+            return dx, None, None, dres, None, None, None, None, None, None, None, None, None
+        return dx, dgamma, dbeta, dres, None, None, None, None, None, None, None, None, None
 
 
 class BNReLU1d(nn.Module):
@@ -98,7 +103,17 @@ class BNReLU1d(nn.Module):
             self._ws = (torch.zeros(4 * c, dtype=torch.float32, device=device), torch.zeros(2, dtype=torch.int32, device=device))
         return self._ws
 
-    def forward(self, x: torch.Tensor, residual: Optional[torch.Tensor] = None) -> torch.Tensor:
+    def stats_request(self, device) -> dict:
+        """What a producing convolution needs to compute this layer's training statistics in its own epilogue
+        (``Conv1dB200.forward(x, bn_req=...)``); pass the dict back to :meth:`forward` as ``stats``."""
+        c = self.weight.numel()
+        acc, ticket = self._workspace(device)
+        buf = torch.empty(4 * c, dtype=torch.float32, device=device)
+        return {"acc": acc[:2 * c], "ticket": ticket[:1], "mean": buf[:c], "rstd": buf[c:2 * c], "coef": buf[2 * c:],
+                "rm": self.running_mean, "rv": self.running_var, "eps": self.eps, "momentum": self.momentum,
+                "gamma": self.weight.detach().float().contiguous(), "beta": self.bias.detach().float().contiguous(), "done": False}
+
+    def forward(self, x: torch.Tensor, residual: Optional[torch.Tensor] = None, stats: Optional[dict] = None) -> torch.Tensor:
         if not x.is_cuda:
             y = F.batch_norm(x, self.running_mean, self.running_var, self.weight, self.bias, self.training,
                              self.momentum, self.eps)
@@ -108,7 +123,8 @@ class BNReLU1d(nn.Module):
         ws = self._workspace(x.device)
         if self.training:
             return _BNAct.apply(x, self.weight, self.bias, residual, self.relu, self.eps, None, None,
-                                (self.running_mean, self.running_var), self.momentum, ws, self)
+                                (self.running_mean, self.running_var), self.momentum, ws, self,
+                                stats if (stats is not None and stats.get("done")) else None)
         return _BNAct.apply(x, self.weight, self.bias, residual, self.relu, self.eps, self.running_mean, self.running_var,
                             None, self.momentum, ws, self)
 
@@ -130,6 +146,15 @@ class _GlobalAvgPool(torch.autograd.Function):
         _lib.check(_lib.cuda_lib().cs_avgpool_bwd(dout.contiguous().float().data_ptr(), dx.data_ptr(), b, l, c, _lib.stream_ptr()),
                    "cs_avgpool_bwd")
         return dx
+
+
+def conv_bn(conv, bn: "BNReLU1d", x: torch.Tensor, residual: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``bn(conv(x), residual)``; in training on CUDA the convolution's epilogue also produces the BN statistics of
+    its output (wide layers), so the separate statistics pass over the activation disappears."""
+    if x.is_cuda and bn.training and conv.cin > 1 and torch.is_grad_enabled():
+        req = bn.stats_request(x.device)
+        return bn(conv(x, bn_req=req), residual, stats=req)
+    return bn(conv(x), residual)
 
 
 def global_avg_pool1d(x: torch.Tensor) -> torch.Tensor:

@@ -74,6 +74,8 @@ size_t comm_bytes(cs_comm*);
 
 int conv1d_fwd(const void*, const void*, const float*, void*, int, int, int, int, int, int, int, int, cudaStream_t);
 int conv1d_dgrad_direct(const void*, const void*, void*, int, int, int, int, int, int, cudaStream_t);
+int conv1d_fwd_bn(const void*, const void*, const float*, void*, int, int, int, int, int, int, int, float*, int32_t*, float*, float*, float*, float*,
+                  float, float, const float*, const float*, float*, cudaStream_t);
 int conv1d_prepare_dgrad_weight(const void*, void*, int, int, int, cudaStream_t);
 int conv1d_wgrad(const void*, const void*, float*, float*, int, int, int, int, int, int, int, cudaStream_t);
 int conv1d_cin1_fwd(const float*, const float*, const float*, void*, int, int, int, int, int, int, int, cudaStream_t);
@@ -171,6 +173,14 @@ int cs_conv1d_dgrad(const void* dy, const void* wt, void* dx, int B, int L, int 
     CS_REQUIRE(stride == 1, "conv1d_dgrad: stride %d not supported by the implicit-GEMM path", stride);
     const int Lout = L + 2 * pad - K + 1;
     return conv1d_fwd(dy, wt, nullptr, dx, B, Lout, Cout, Cin, K, K - 1 - pad, 1, 0, ST(s));
+}
+int cs_conv1d_fwd_bn(const void* x, const void* w, const float* bias, void* y, int B, int L, int Cin, int Cout, int K, int pad,
+                     int stride, int relu, float* acc, int32_t* ticket, float* mean, float* rstd, float* running_mean,
+                     float* running_var, float eps, float momentum, const float* gamma, const float* beta, float* coef,
+                     cs_stream_t s) {
+    if (stride != 1) return CS_ERR_UNSUPPORTED;
+    return conv1d_fwd_bn(x, w, bias, y, B, L, Cin, Cout, K, pad, relu, acc, ticket, mean, rstd, running_mean, running_var, eps,
+                         momentum, gamma, beta, coef, ST(s));
 }
 int cs_conv1d_dgrad_direct(const void* dy, const void* w, void* dx, int B, int L, int Cin, int Cout, int K, int pad,
                            int stride, cs_stream_t s) {

@@ -48,6 +48,39 @@ __device__ __forceinline__ float warp_sum(float v) {
     return v;
 }
 
+// ---- BatchNorm statistics tail (shared by bn_stats_kernel and the conv forward epilogue) ------------------------
+// Run by the LAST block to arrive on `ticket`: the per-channel totals are complete in `stats` (L2 atomics), so that
+// block turns them into the layer's outputs and CLEARS the accumulators — a persistent, self-cleaning workspace.
+struct BnStatsTail {
+    int32_t* ticket;          // nullptr: plain accumulate-only kernel
+    float* mean; float* rstd; float* running_mean; float* running_var;
+    float rows, eps, momentum;
+    const float* gamma; const float* beta; float* coef;   // optional: coef[0:C] = rstd*gamma, coef[C:2C] = beta - mean*rstd*gamma
+};
+
+__device__ __forceinline__ void bn_stats_tail_channels(float* stats, int C, const BnStatsTail& t, int tid, int nthreads) {
+    for (int c = tid; c < C; c += nthreads) {
+        // every load of the tail is issued before the first use: one L2 round trip, not four
+        const float s0 = __ldcg(stats + c), s1 = __ldcg(stats + C + c);
+        const float rm = t.running_mean ? t.running_mean[c] : 0.0f, rv = t.running_mean ? t.running_var[c] : 0.0f;
+        const float ga = t.coef ? t.gamma[c] : 0.0f, be = t.coef ? t.beta[c] : 0.0f;
+        const float m = s0 / t.rows;
+        const float var = fmaxf(s1 / t.rows - m * m, 0.0f);
+        const float rs = rsqrtf(var + t.eps);
+        t.mean[c] = m;
+        t.rstd[c] = rs;
+        if (t.running_mean) {
+            t.running_mean[c] = rm + t.momentum * (m - rm);
+            t.running_var[c] = rv + t.momentum * (var * (t.rows / fmaxf(t.rows - 1.0f, 1.0f)) - rv);
+        }
+        if (t.coef) {
+            t.coef[c] = rs * ga;
+            t.coef[C + c] = be - m * rs * ga;
+        }
+        stats[c] = 0.0f; stats[C + c] = 0.0f;
+    }
+}
+
 __device__ __forceinline__ bool finite_f(float v) { return fabsf(v) <= 3.402823466e38f; }
 
 }  // namespace cs

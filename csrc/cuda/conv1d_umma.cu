@@ -218,8 +218,12 @@ conv1d_fwd_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
     if (warp == 1) tmem_dealloc(tmem_base, tmem_cols);
 }
 
+struct ConvBnArgs {      // host-side bundle for the fused output statistics (see Fwd128Shape::bn_acc)
+    float* acc; int32_t* ticket; float* mean; float* rstd; float* running_mean; float* running_var;
+    float eps, momentum; const float* gamma; const float* beta; float* coef;
+};
 static int conv1d_fwd_sw128(const void* x, const void* w, const float* bias, void* y, int B, int L, int Cin, int Cout, int K,
-                            int pad, int relu, int Lout, cudaStream_t st, int wmn = 0);
+                            int pad, int relu, int Lout, cudaStream_t st, int wmn = 0, const ConvBnArgs* bn = nullptr);
 static int pick_ck(int C) { return C % 64 == 0 ? 64 : (C % 32 == 0 ? 32 : 16); }
 static int pick_nt(int C) { return C % 128 == 0 ? 128 : (C % 64 == 0 ? 64 : (C % 32 == 0 ? 32 : 16)); }
 
@@ -307,6 +311,12 @@ struct Fwd128Shape {
                              // is an MN-major B operand and the taps are read in reverse — no transposed copy of w
     int slot;                // 0, or 32 / 64: short windows (Lout + K - 1 <= slot), a tile packs 128/slot whole samples, each
                              // in its own `slot` rows (the taps of one sample never reach the next sample's outputs)
+    // fused BatchNorm statistics of the OUTPUT (training mode): per-channel sum / sum of squares of the bf16 values
+    // this kernel stores, accumulated into bn_acc[2 * Cout]; the last CTA to arrive turns them into mean / rstd /
+    // running statistics / affine coefficients and clears the workspace (same contract as cs_bn_stats_finalize)
+    float* bn_acc;           // nullptr: no statistics
+    int bn_arrivals;         // CTAs that reach the ticket
+    BnStatsTail bn;
 };
 
 constexpr int kMaxWStages = 8;
@@ -468,12 +478,18 @@ __device__ __forceinline__ void conv1d_fwd_sw128_body(const CUtensorMap& map_x, 
             // two 4 KB slabs per warp inside the (now idle) activation ring; slab row r = accumulator lane
             uint8_t* slabs = a_ring + q * 8192;
             int n_store = 0;
+            // BN statistics: this lane's channel pair of each 64-channel block, kept in the (idle) weight ring:
+            // [warp][64-channel block][channel][sum, sumsq] — lane-private entries until the warps meet below
+            float* red = reinterpret_cast<float*>(w_ring);
+            if (s.bn_acc)
+                for (int h4 = 0; h4 * 64 < s.NT; ++h4)
+                    *reinterpret_cast<float4*>(red + ((q * 4 + h4) * 64 + 2 * lane) * 2) = make_float4(0.f, 0.f, 0.f, 0.f);
             for (int i = 0; i < s.MT; ++i) {
                 const int t = t0 + i;
                 int tb = t / s.tiles, tl = (t % s.tiles) * 128 + q * 32;
                 if (s.slot) { tb = t * (128 / s.slot) + (q * 32) / s.slot; tl = (q * 32) % s.slot; }
                 if (t >= s.total || tl >= s.Lout || tb >= s.B) continue;
-                for (int hh = 0; hh < s.NT; hh += 64, ++n_store) {
+                for (int hh = 0; hh < s.NT; hh += 64) {
                     uint8_t* slab = slabs + (n_store & 1) * 4096;
                     uint32_t v[64];
                     const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + i * s.NT + hh;
@@ -503,10 +519,57 @@ __device__ __forceinline__ void conv1d_fwd_sw128_body(const CUtensorMap& map_x, 
                         tma_store_3d(&map_y, slab, n0 + hh, tl, tb);     // rows past Lout are clipped by the map
                         tma_store_commit();
                     }
+                    ++n_store;
+                    if (s.bn_acc) {
+                        // column sums of the slab just written (the stored bf16 values, rows inside the sample only):
+                        // lane = channel pair (2*lane, 2*lane+1) -> 16-byte chunk lane/4, word lane%4 of every row
+                        const int valid = s.Lout - tl < 32 ? s.Lout - tl : 32;
+                        float a0 = 0.f, a1 = 0.f, q0 = 0.f, q1 = 0.f;
+                        for (int r0 = 0; r0 < 32; r0 += 8) {           // 8 independent loads in flight (rows r0 .. r0+7)
+                            uint32_t u[8];
+#pragma unroll
+                            for (int j = 0; j < 8; ++j)                // (r0 + j) & 7 == j: the swizzle phase is the unroll index
+                                u[j] = (r0 + j < valid)
+                                           ? *reinterpret_cast<const uint32_t*>(slab + (r0 + j) * 128 + (((lane >> 2) ^ j) << 4) + (lane & 3) * 4)
+                                           : 0u;
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) {
+                                const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&u[j]));
+                                a0 += f.x; q0 = fmaf(f.x, f.x, q0); a1 += f.y; q1 = fmaf(f.y, f.y, q1);
+                            }
+                        }
+                        float4* p = reinterpret_cast<float4*>(red + ((q * 4 + (hh >> 6)) * 64 + 2 * lane) * 2);
+                        float4 cur = *p;
+                        cur.x += a0; cur.y += q0; cur.z += a1; cur.w += q1;
+                        *p = cur;
+                    }
                 }
             }
             if (lane == 0) tma_store_wait_read<0>();
             __syncwarp();
+            if (s.bn_acc) {
+                // the four epilogue warps meet in the idle weight ring: [warp][64-channel block][channel][sum, sumsq],
+                // then ONE atomic per channel and quantity per CTA; the last CTA to arrive finishes the layer statistics
+                const int et = threadIdx.x - 64;             // 0..127 over warps 2..5
+                volatile uint32_t* last_flag = tmem_slot + 1;
+                asm volatile("bar.sync 1, 128;" ::: "memory");
+                for (int o = et; o < s.NT * 2; o += 128) {
+                    const int ch = o >> 1, qty = o & 1;
+                    float v = 0.0f;
+#pragma unroll
+                    for (int w = 0; w < 4; ++w) v += red[((w * 4 + (ch >> 6)) * 64 + (ch & 63)) * 2 + qty];
+                    atomicAdd(s.bn_acc + qty * s.Cout + n0 + ch, v);
+                }
+                __threadfence();
+                asm volatile("bar.sync 1, 128;" ::: "memory");
+                if (et == 0) *last_flag = (atomicAdd(s.bn.ticket, 1) == s.bn_arrivals - 1) ? 1u : 0u;
+                asm volatile("bar.sync 1, 128;" ::: "memory");
+                if (*last_flag) {
+                    __threadfence();
+                    bn_stats_tail_channels(s.bn_acc, s.Cout, s.bn, et, 128);
+                    if (et == 0) *s.bn.ticket = 0;
+                }
+            }
         } else {
             for (int i = 0; i < s.MT; ++i) {
                 const int t = t0 + i;
@@ -547,14 +610,15 @@ __device__ __forceinline__ void conv1d_fwd_sw128_body(const CUtensorMap& map_x, 
     }
 }
 
-__global__ void __launch_bounds__(kFwdThreads, 1)
+// (launch bound 2: two of these CTAs must fit one SM's register file — 168 registers per thread at most)
+__global__ void __launch_bounds__(kFwdThreads, 2)
 conv1d_fwd_sw128_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_w,
                         const __grid_constant__ CUtensorMap map_y, const __grid_constant__ CUtensorMap map_xs,
                         const float* __restrict__ bias, __nv_bfloat16* __restrict__ y, const Fwd128Shape s) {
     conv1d_fwd_sw128_body<false>(map_x, map_w, map_y, map_xs, bias, y, s);
 }
 
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kFwdThreads, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kFwdThreads, 2)
 conv1d_fwd_pair_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_w,
                        const __grid_constant__ CUtensorMap map_y, const __grid_constant__ CUtensorMap map_xs,
                        const float* __restrict__ bias, __nv_bfloat16* __restrict__ y, const Fwd128Shape s) {
@@ -570,10 +634,11 @@ static int env_int(const char* name, int dflt) {
 // Tuning overrides for experiments: CS_CONV_SW128=0 (use the plane kernel), CS_CONV_PAIR=0 (no cta_group::2 pairs),
 // CS_CONV_MT / CS_CONV_AS / CS_CONV_WS.
 static int conv1d_fwd_sw128(const void* x, const void* w, const float* bias, void* y, int B, int L, int Cin, int Cout, int K,
-                            int pad, int relu, int Lout, cudaStream_t st, int wmn) {
+                            int pad, int relu, int Lout, cudaStream_t st, int wmn, const ConvBnArgs* bn) {
     if (Cin % 64 != 0 || Cout % 32 != 0 || Lout + K - 1 <= 16 || !env_int("CS_CONV_SW128", 1)) return -1;
     if (wmn && Cout % 64 != 0) return -1;
     Fwd128Shape s;
+    memset(&s, 0, sizeof(s));
     s.wmn = wmn;
     s.B = B; s.L = L; s.Lout = Lout; s.Cin = Cin; s.Cout = Cout; s.K = K; s.pad = pad; s.relu = relu;
     s.R = 128 + K - 1;
@@ -663,6 +728,13 @@ static int conv1d_fwd_sw128(const void* x, const void* w, const float* bias, voi
     }
     int units = (s.total + s.MT - 1) / s.MT;
     if (pair) units = (units + 1) & ~1;                      // whole pairs; the odd one out loads zeros and stores nothing
+    if (bn) {
+        if (!s.tma_store) return -1;                         // statistics are taken from the shared-memory slabs
+        s.bn_acc = bn->acc;
+        s.bn_arrivals = (Cout / s.NT) * units;               // every CTA that does not return early
+        s.bn = BnStatsTail{bn->ticket, bn->mean, bn->rstd, bn->running_mean, bn->running_var, (float)((double)B * Lout), bn->eps,
+                           bn->momentum, bn->gamma, bn->beta, bn->coef};
+    }
     int gy = units < 32768 ? units : 32768;
     dim3 grid(Cout / s.NT, gy, (units + gy - 1) / gy);
     if (pair) grid = dim3(units, Cout / s.NT, 1);
@@ -686,6 +758,24 @@ static int conv1d_fwd_sw128(const void* x, const void* w, const float* bias, voi
     else conv1d_fwd_pair_kernel<<<grid, kFwdThreads, smem, st>>>(mx, mw, my, mxs, bias, (__nv_bfloat16*)y, s);   // cluster (2,1,1)
     CS_CUDA_OK(cudaGetLastError());
     return CS_OK;
+}
+
+// conv forward + training-mode BatchNorm statistics of its output in one launch (wide layers only).
+// CS_ERR_UNSUPPORTED (nothing launched) when the shape is not on the slab-epilogue path: run cs_conv1d_fwd and
+// cs_bn_stats_finalize instead.
+int conv1d_fwd_bn(const void* x, const void* w, const float* bias, void* y, int B, int L, int Cin, int Cout, int K, int pad, int relu,
+                  float* acc, int32_t* ticket, float* mean, float* rstd, float* rm, float* rv, float eps, float momentum,
+                  const float* gamma, const float* beta, float* coef, cudaStream_t st) {
+    CS_REQUIRE(K >= 1 && K <= 64 && pad >= 0 && pad < K, "conv1d: bad K=%d pad=%d", K, pad);
+    CS_REQUIRE((((uintptr_t)x | (uintptr_t)w | (uintptr_t)y) & 15) == 0, "conv1d: pointers must be 16-byte aligned");
+    CS_REQUIRE(acc && ticket && mean && rstd, "conv1d_fwd_bn: null workspace / output");
+    CS_REQUIRE(coef == nullptr || (gamma && beta), "conv1d_fwd_bn: coef needs gamma and beta");
+    CS_REQUIRE((rm == nullptr) == (rv == nullptr), "conv1d_fwd_bn: give both running statistics or neither");
+    const int Lout = L + 2 * pad - K + 1;
+    if (Lout < 1 || !env_int("CS_CONV_BN_FUSE", 1)) return CS_ERR_UNSUPPORTED;
+    ConvBnArgs bn{acc, ticket, mean, rstd, rm, rv, eps, momentum, gamma, beta, coef};
+    const int rc = conv1d_fwd_sw128(x, w, bias, y, B, L, Cin, Cout, K, pad, relu, Lout, st, 0, &bn);
+    return rc < 0 ? CS_ERR_UNSUPPORTED : rc;
 }
 
 // dx = conv(dy, flipped/transposed w) computed from the forward weights themselves (see Fwd128Shape::wmn).

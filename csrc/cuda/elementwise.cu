@@ -248,12 +248,7 @@ __device__ __forceinline__ void column_reduce_finish(float (&acc)[Q][8], float* 
 // Optional tail of the two column reductions below, run by the LAST block to arrive (ticket): the per-channel totals
 // are complete in `acc` (L2 atomics), so that block turns them into the layer's outputs and then CLEARS acc and the
 // ticket — the accumulator is a persistent, self-cleaning workspace and no fill / finalize / add launches are needed.
-struct BnStatsTail {
-    int32_t* ticket;          // nullptr: plain accumulate-only kernel (cs_bn_stats / cs_bn_bwd_reduce)
-    float* mean; float* rstd; float* running_mean; float* running_var;
-    float rows, eps, momentum;
-    const float* gamma; const float* beta; float* coef;   // optional: coef[0:C] = rstd*gamma, coef[C:2C] = beta - mean*rstd*gamma
-};
+// (BnStatsTail and bn_stats_tail_channels live in common/cs_common.cuh: the conv epilogue shares them)
 struct BnBwdTail {
     int32_t* ticket;
     float* dgamma; float* dbeta;          // this batch's reductions
@@ -297,26 +292,7 @@ __global__ void __launch_bounds__(kRedThreads) bn_stats_kernel(const uint4* __re
     float* const out[2] = {stats, stats + C};
     column_reduce_finish<2>(acc, out, C, g, rl, rpb, sm_red);
     if (t.ticket == nullptr || !last_block_arrives(t.ticket)) return;
-    for (int c = threadIdx.x; c < C; c += blockDim.x) {
-        // every load of the tail is issued before the first use: one L2 round trip, not four
-        const float s0 = __ldcg(stats + c), s1 = __ldcg(stats + C + c);
-        const float rm = t.running_mean ? t.running_mean[c] : 0.0f, rv = t.running_mean ? t.running_var[c] : 0.0f;
-        const float ga = t.coef ? t.gamma[c] : 0.0f, be = t.coef ? t.beta[c] : 0.0f;
-        const float m = s0 / t.rows;
-        const float var = fmaxf(s1 / t.rows - m * m, 0.0f);
-        const float rs = rsqrtf(var + t.eps);
-        t.mean[c] = m;
-        t.rstd[c] = rs;
-        if (t.running_mean) {
-            t.running_mean[c] = rm + t.momentum * (m - rm);
-            t.running_var[c] = rv + t.momentum * (var * (t.rows / fmaxf(t.rows - 1.0f, 1.0f)) - rv);
-        }
-        if (t.coef) {
-            t.coef[c] = rs * ga;
-            t.coef[C + c] = be - m * rs * ga;
-        }
-        stats[c] = 0.0f; stats[C + c] = 0.0f;
-    }
+    bn_stats_tail_channels(stats, C, t, threadIdx.x, blockDim.x);
     if (threadIdx.x == 0) *t.ticket = 0;
 }
 

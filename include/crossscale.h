@@ -130,6 +130,17 @@ int cs_sgd_momentum(float* p, float* mom, const float* g, int64_t n, float lr, f
  * ------------------------------------------------------------------------------------------- */
 int cs_conv1d_fwd(const void* x, const void* w, const float* bias, void* y, int B, int L, int Cin,
                   int Cout, int K, int pad, int stride, int relu, cs_stream_t stream);
+/* cs_conv1d_fwd + the training-mode BatchNorm statistics of its output in ONE launch: the epilogue sums the
+ * bf16 values it stores per channel, and the last CTA to finish turns the totals into mean / rstd / running
+ * statistics / affine coefficients exactly like cs_bn_stats_finalize (same persistent workspace contract:
+ * acc [2*Cout] fp32 + ticket [1] int32, zero before the first call, left zero).  Wide layers only
+ * (Cin % 64 == 0, Cout % 64 == 0): returns CS_ERR_UNSUPPORTED and launches nothing otherwise — then call
+ * cs_conv1d_fwd followed by cs_bn_stats_finalize. */
+int cs_conv1d_fwd_bn(const void* x, const void* w, const float* bias, void* y, int B, int L, int Cin,
+                     int Cout, int K, int pad, int stride, int relu, float* acc, int32_t* ticket,
+                     float* mean, float* rstd, float* running_mean, float* running_var, float eps,
+                     float momentum, const float* gamma, const float* beta, float* coef,
+                     cs_stream_t stream);
 /* dx = conv_transpose(dy, w):  dy [B,Lout,Cout] bf16 -> dx [B,L,Cin] bf16.  wt is the
  * tap-flipped, channel-transposed weight [K, Cin, Cout] (cs_conv1d_prepare_dgrad_weight). */
 int cs_conv1d_dgrad(const void* dy, const void* wt, void* dx, int B, int L, int Cin, int Cout,

@@ -157,6 +157,42 @@ def test_bn_workspace_is_self_cleaning_and_grads_can_go_straight_to_the_arena():
         assert _rel(a, b) < 1e-5
 
 
+@pytest.mark.parametrize("B,L,Cin,Cout,K", [(6, 360, 64, 128, 7), (9, 45, 128, 256, 7), (3, 130, 256, 512, 3), (5, 200, 64, 64, 5)])
+def test_conv_epilogue_produces_the_bn_statistics(B, L, Cin, Cout, K):
+    """conv_bn (statistics summed in the convolution's epilogue, finished by its last CTA) against conv followed by the
+    separate statistics kernel: same outputs, running statistics and gradients; the workspace is left zero"""
+    import copy
+    from crossscale.ops.conv1d import Conv1dB200
+    from crossscale.ops.norm_act import BNReLU1d, conv_bn
+    torch.manual_seed(B + K)
+    conv = Conv1dB200(Cin, Cout, K, padding=K // 2, bias=False).to(DEV)
+    with torch.no_grad():
+        conv.weight.copy_(_bf(conv.weight))
+    bns = [BNReLU1d(Cout, relu=True).to(DEV) for _ in range(2)]
+    with torch.no_grad():
+        bns[0].weight.copy_(torch.rand(Cout, device=DEV) + 0.5); bns[0].bias.copy_(torch.randn(Cout, device=DEV) * 0.1)
+    bns[1].load_state_dict(copy.deepcopy(bns[0].state_dict()))
+    x = _bf(torch.randn(B, L, Cin, device=DEV)).to(torch.bfloat16)
+    res = _bf(torch.randn(B, L, Cout, device=DEV)).to(torch.bfloat16)
+    dy = _bf(torch.randn(B, L, Cout, device=DEV)).to(torch.bfloat16)
+    outs = []
+    for fused, bn in zip((False, True), bns):
+        conv.weight.grad = None
+        xi = x.clone().requires_grad_(True)
+        y = conv_bn(conv, bn, xi, residual=res) if fused else bn(conv(xi), res)
+        y.backward(dy)
+        torch.cuda.synchronize()
+        acc, ticket = bn._ws
+        assert float(acc.abs().max()) == 0.0 and int(ticket.abs().max()) == 0
+        outs.append((y.float(), xi.grad.float(), conv.weight.grad.clone(), bn.weight.grad.clone(), bn.bias.grad.clone(),
+                     bn.running_mean.clone(), bn.running_var.clone()))
+    for a, b in zip(*outs):
+        assert _rel(a, b) < 2e-3, (_rel(a, b))
+    yr = F.batch_norm(F.conv1d(x.float().permute(0, 2, 1), conv.weight_oik.detach(), padding=K // 2), None, None, bns[0].weight.detach(),
+                      bns[0].bias.detach(), True, 0.1, 1e-5)
+    assert _rel(outs[1][0].permute(0, 2, 1), F.relu(yr + res.float().permute(0, 2, 1))) < 1.5e-2
+
+
 def test_pool_and_layout_kernels():
     from crossscale.ops import _lib
     from crossscale.ops.norm_act import global_avg_pool1d
