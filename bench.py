@@ -26,7 +26,7 @@ sys.path.insert(0, REPO)
 
 METRIC = "ECG samples/sec per FL round (TinyECG FedAvg, aggregation included)"
 BATCH, LOCAL_STEPS, WIN_LEN, NUM_CLASSES = 256, 50, 500, 2
-PREHEAT_S = 0.25        # untimed spin-up before the warm-up rounds (see run_ours)
+PREHEAT_ROUNDS = 304    # untimed spin-up rounds (~0.25 s) before the warm-up rounds (see run_ours)
 # 131072 windows x 500 x 4 B = 262 MB per client: larger than the 126 MB L2, so the random-batch
 # gather of every round comes from HBM (timing rule: inputs larger than L2).
 NUM_WINDOWS = 131072
@@ -101,21 +101,28 @@ def run_ours(args):
         torch.cuda.synchronize()
 
     # ---- device-timed rounds (GPU-resident data, like the reference) ----------------------------
+    # one nvidia-smi poller for the job (rank 0's GPU; eight of them contend for the driver with the launching threads).
+    # It is started BEFORE the pre-heat and given time to deliver its first sample: nvidia-smi's start-up (NVML init,
+    # driver queries) can stall kernel launches for milliseconds, which is a large share of a 16 ms timed region
+    # (seen as occasional 0.99-1.04 ms rounds instead of 0.81-0.83 when it was started right before the timed loop).
+    sampler = ClockSampler(gpu_index=torch.cuda.current_device())
+    if rank == 0:
+        sampler.start()
+        t_wait = time.perf_counter()
+        while sampler.proc is not None and not sampler.lines and time.perf_counter() - t_wait < 2.0:
+            time.sleep(0.01)
+    sync_all()
     # pre-heat: a GPU that sat idle while Python started takes tens of ms to reach its boost clocks, longer than the
-    # W warm-up rounds (W * 0.8 ms); spin untimed rounds for ~0.25 s first so the timed rounds see steady clocks
-    t_heat = time.perf_counter()
-    while time.perf_counter() - t_heat < PREHEAT_S:
-        for _ in range(8):
-            runner.run_round_async()
-        torch.cuda.synchronize()
+    # W warm-up rounds (W * 0.8 ms); spin ~0.25 s of untimed rounds first so the timed rounds see steady clocks
+    # (a fixed COUNT, not a wall-clock loop: every rank must run the same number of aggregation rounds)
+    for i in range(PREHEAT_ROUNDS):
+        runner.run_round_async()
+        if i % 16 == 15:
+            torch.cuda.synchronize()
     for _ in range(W):
         runner.run_round_async()
     sync_all()
     launches0 = runner.trainer.launches + runner.agg.launches
-    # one nvidia-smi poller for the job (rank 0's GPU): eight of them contend for the driver with the launching threads
-    sampler = ClockSampler(gpu_index=torch.cuda.current_device())
-    if rank == 0:
-        sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(K):
@@ -204,7 +211,7 @@ def run_ours(args):
                        "windows_per_client": args.num_windows,
                        "l2": "inputs larger than L2 (262 MB resident dataset per client, random gather)",
                        "aggregation": runner.agg.backend,
-                       "preheat": f"{PREHEAT_S} s of untimed rounds before the {W} warm-up rounds (clock ramp from idle)"},
+                       "preheat": f"{PREHEAT_ROUNDS} untimed rounds (~0.25 s) before the {W} warm-up rounds (clock ramp from idle)"},
             "exposed_agg_ms_per_round": agg_ms, "avg_loss": loss_dev / max(1, (W + K) * LOCAL_STEPS),
             "clocks": clocks, "gpu_launches": int(launches), "comm_status": status,
         }
