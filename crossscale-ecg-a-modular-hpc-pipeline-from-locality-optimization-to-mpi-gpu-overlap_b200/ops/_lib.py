@@ -37,6 +37,7 @@ _CUDA_SIGS = {
     "cs_conv1d_fwd": (i32, [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, vp]),
     "cs_conv1d_dgrad": (i32, [vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp]),
     "cs_conv1d_fwd_bn": (i32, [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, vp, vp, vp, vp, vp, vp, f32, f32, vp, vp, vp, vp]),
+    "cs_conv1d_plan": (i32, [i32, i32, i32, i32, i32, i32, i32, vp]),
     "cs_conv1d_dgrad_direct": (i32, [vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp]),
     "cs_conv1d_prepare_dgrad_weight": (i32, [vp, vp, i32, i32, i32, vp]),
     "cs_conv1d_wgrad": (i32, [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp]),

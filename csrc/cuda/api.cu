@@ -74,6 +74,7 @@ size_t comm_bytes(cs_comm*);
 
 int conv1d_fwd(const void*, const void*, const float*, void*, int, int, int, int, int, int, int, int, cudaStream_t);
 int conv1d_dgrad_direct(const void*, const void*, void*, int, int, int, int, int, int, cudaStream_t);
+int conv1d_plan(int, int, int, int, int, int, int, int*);
 int conv1d_fwd_bn(const void*, const void*, const float*, void*, int, int, int, int, int, int, int, float*, int32_t*, float*, float*, float*, float*,
                   float, float, const float*, const float*, float*, cudaStream_t);
 int conv1d_prepare_dgrad_weight(const void*, void*, int, int, int, cudaStream_t);
@@ -181,6 +182,9 @@ int cs_conv1d_fwd_bn(const void* x, const void* w, const float* bias, void* y, i
     if (stride != 1) return CS_ERR_UNSUPPORTED;
     return conv1d_fwd_bn(x, w, bias, y, B, L, Cin, Cout, K, pad, relu, acc, ticket, mean, rstd, running_mean, running_var, eps,
                          momentum, gamma, beta, coef, ST(s));
+}
+int cs_conv1d_plan(int B, int L, int Cin, int Cout, int K, int pad, int direction, int* out16) {
+    return conv1d_plan(B, L, Cin, Cout, K, pad, direction, out16);
 }
 int cs_conv1d_dgrad_direct(const void* dy, const void* w, void* dx, int B, int L, int Cin, int Cout, int K, int pad,
                            int stride, cs_stream_t s) {

@@ -351,14 +351,15 @@ conv1d_fwd_pair_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_c
 // Launches the 128-byte-row variant and returns CS_OK (or an error), or -1 when the shape is not one it covers.
 // Tuning overrides for experiments: CS_CONV_SW128=0 (use the plane kernel), CS_CONV_PAIR=0 (no cta_group::2 pairs),
 // CS_CONV_MT / CS_CONV_AS / CS_CONV_WS.
-int conv1d_fwd_sw128(const void* x, const void* w, const float* bias, void* y, int B, int L, int Cin, int Cout, int K, int pad,
-                     int relu, int Lout, cudaStream_t st, int wmn, const ConvBnArgs* bn) {
+// Host-side choice of kernel variant and tile configuration (pure arithmetic: also reachable through cs_conv1d_plan,
+// which the CPU tests use to check the resource invariants).  Returns 0, or -1 when the shape is not covered.
+static int plan_fwd128(int B, int L, int Cin, int Cout, int K, int pad, int Lout, int wmn, Fwd128Shape& s, int& pair, size_t& smem,
+                       dim3& grid, int& units) {
     if (Cin % 64 != 0 || Cout % 32 != 0 || Lout + K - 1 <= 16 || !env_int("CS_CONV_SW128", 1)) return -1;
     if (wmn && Cout % 64 != 0) return -1;
-    Fwd128Shape s;
     memset(&s, 0, sizeof(s));
     s.wmn = wmn;
-    s.B = B; s.L = L; s.Lout = Lout; s.Cin = Cin; s.Cout = Cout; s.K = K; s.pad = pad; s.relu = relu;
+    s.B = B; s.L = L; s.Lout = Lout; s.Cin = Cin; s.Cout = Cout; s.K = K; s.pad = pad; 
     s.R = 128 + K - 1;
     s.tile_stride = (s.R * 128 + 1023) & ~1023;
     s.tiles = (Lout + 127) / 128;
@@ -370,7 +371,7 @@ int conv1d_fwd_sw128(const void* x, const void* w, const float* bias, void* y, i
         s.total = (B + 128 / s.slot - 1) / (128 / s.slot);
     }
     const size_t kHalfSm = 113 * 1024, kFullSm = 227 * 1024;
-    int pair = 0;
+    pair = 0;
     auto need = [&]() {
         return (size_t)2048 + (size_t)s.AS * s.tile_stride * s.MT + (size_t)s.WS * (pair ? s.NT / 2 : s.NT) * 128;
     };
@@ -415,6 +416,23 @@ int conv1d_fwd_sw128(const void* x, const void* w, const float* bias, void* y, i
     { const int v = env_int("CS_CONV_WS", 0); if (v >= 2 && v <= kMaxWStages) s.WS = v; }
     if (need() > kFullSm) return -1;
     s.tma_store = (s.NT % 64 == 0 && (size_t)s.AS * s.tile_stride * s.MT >= 32768 && env_int("CS_CONV_TMA_STORE", 1)) ? 1 : 0;
+    smem = need();
+    units = (s.total + s.MT - 1) / s.MT;
+    if (pair) units = (units + 1) & ~1;                      // whole pairs; the odd one out loads zeros and stores nothing
+    const int gy = units < 32768 ? units : 32768;
+    grid = dim3(Cout / s.NT, gy, (units + gy - 1) / gy);
+    if (pair) grid = dim3(units, Cout / s.NT, 1);            // pairs are neighbours along x
+    return 0;
+}
+
+int conv1d_fwd_sw128(const void* x, const void* w, const float* bias, void* y, int B, int L, int Cin, int Cout, int K, int pad,
+                     int relu, int Lout, cudaStream_t st, int wmn, const ConvBnArgs* bn) {
+    Fwd128Shape s;
+    int pair = 0, units = 0;
+    size_t smem = 0;
+    dim3 grid;
+    if (plan_fwd128(B, L, Cin, Cout, K, pad, Lout, wmn, s, pair, smem, grid, units) != 0) return -1;
+    s.relu = relu;
     const int w_rows = pair ? s.NT / 2 : s.NT;
     CUtensorMap mx, mw;
     int rc = make_row_map(&mx, x, B, L, Cin, s.R);
@@ -430,7 +448,6 @@ int conv1d_fwd_sw128(const void* x, const void* w, const float* bias, void* y, i
         rc = make_row_map(&mxs, x, B, L, Cin, s.slot);
         if (rc) return rc;
     }
-    const size_t smem = need();
     static size_t configured[2][64] = {};
     int dev = 0;
     CS_CUDA_OK(cudaGetDevice(&dev));
@@ -444,8 +461,6 @@ int conv1d_fwd_sw128(const void* x, const void* w, const float* bias, void* y, i
         }
         configured[pair][dev & 63] = smem;
     }
-    int units = (s.total + s.MT - 1) / s.MT;
-    if (pair) units = (units + 1) & ~1;                      // whole pairs; the odd one out loads zeros and stores nothing
     if (bn) {
         if (!s.tma_store) return -1;                         // statistics are taken from the shared-memory slabs
         s.bn_acc = bn->acc;
@@ -453,9 +468,6 @@ int conv1d_fwd_sw128(const void* x, const void* w, const float* bias, void* y, i
         s.bn = BnStatsTail{bn->ticket, bn->mean, bn->rstd, bn->running_mean, bn->running_var, (float)((double)B * Lout), bn->eps,
                            bn->momentum, bn->gamma, bn->beta, bn->coef};
     }
-    int gy = units < 32768 ? units : 32768;
-    dim3 grid(Cout / s.NT, gy, (units + gy - 1) / gy);
-    if (pair) grid = dim3(units, Cout / s.NT, 1);
     if (env_int("CS_CONV_DEBUG", 0)) {
         int occ = -1;
         if (pair) {
@@ -629,10 +641,8 @@ conv1d_wgrad_sw128_kernel(const __grid_constant__ CUtensorMap map_dy, const __gr
 }
 
 // returns -1 when the shape is outside this variant (the plane kernel handles it)
-int conv1d_wgrad_sw128(const void* x, const void* dy, float* dw, int B, int L, int Cin, int Cout, int K, int pad, int Lout,
-                              cudaStream_t st) {
+static int plan_wgrad128(int B, int L, int Cin, int Cout, int K, int pad, int Lout, Wg128Shape& s, int& passes, size_t& smem, dim3& grid) {
     if (Cin % 64 != 0 || Cout % 64 != 0 || (Cout > 64 && Cout % 128 != 0) || Lout + K - 1 <= 16 || !env_int("CS_CONV_SW128", 1)) return -1;
-    Wg128Shape s;
     memset(&s, 0, sizeof(s));
     s.B = B; s.L = L; s.Lout = Lout; s.Cin = Cin; s.Cout = Cout; s.K = K; s.pad = pad;
     s.tiles_per_sample = (Lout + 127) / 128; s.total_tiles = B * s.tiles_per_sample;
@@ -647,7 +657,7 @@ int conv1d_wgrad_sw128(const void* x, const void* dy, float* dw, int B, int L, i
     s.NC = (K <= 8 && Cin % 128 == 0) ? 128 : 64;
     { const int v = env_int("CS_WGRAD_NC", 0); if ((v == 64 || v == 128) && Cin % v == 0) s.NC = v; }
     s.TP = 512 / s.NC;
-    const int passes = (K + s.TP - 1) / s.TP;
+    passes = (K + s.TP - 1) / s.TP;
     const int gx = (Cout + 127) / 128, gy = Cin / s.NC, outs = gx * gy * passes;
     // Split of the reduction (sample, tile) list.  Every split ends with an atomic flush of its [taps x 128 x NC]
     // partial (256 KB at most), and all CTAs flush at about the same time, so the flush costs ~ splits * outs * c_epi
@@ -667,6 +677,18 @@ int conv1d_wgrad_sw128(const void* x, const void* dy, float* dw, int B, int L, i
     s.S = splits;
     s.R = 128 + (K < s.TP ? K : s.TP) - 1;
     s.x_block = (s.R * 128 + 1023) & ~1023;
+    smem = 2048 + (size_t)kWg128Stages * (2 * 16384 + (size_t)s.x_block * (s.NC / 64));
+    grid = dim3(gx, gy, passes * splits);
+    return 0;
+}
+
+int conv1d_wgrad_sw128(const void* x, const void* dy, float* dw, int B, int L, int Cin, int Cout, int K, int pad, int Lout,
+                       cudaStream_t st) {
+    Wg128Shape s;
+    int passes = 0;
+    size_t smem = 0;
+    dim3 grid;
+    if (plan_wgrad128(B, L, Cin, Cout, K, pad, Lout, s, passes, smem, grid) != 0) return -1;
     CUtensorMap mdy, mx;
     int rc = make_row_map(&mdy, dy, B, Lout, Cout, 128);
     if (rc) return rc;
@@ -679,7 +701,6 @@ int conv1d_wgrad_sw128(const void* x, const void* dy, float* dw, int B, int L, i
         rc = make_row_map(&mxs, x, B, L, Cin, s.slot);
         if (rc) return rc;
     }
-    const size_t smem = 2048 + (size_t)kWg128Stages * (2 * 16384 + (size_t)s.x_block * (s.NC / 64));
     static size_t configured[64] = {};
     int dev = 0;
     CS_CUDA_OK(cudaGetDevice(&dev));
@@ -687,8 +708,44 @@ int conv1d_wgrad_sw128(const void* x, const void* dy, float* dw, int B, int L, i
         CS_CUDA_OK(cudaFuncSetAttribute(conv1d_wgrad_sw128_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured[dev & 63] = smem;
     }
-    conv1d_wgrad_sw128_kernel<<<dim3(gx, gy, passes * splits), kWgThreads, smem, st>>>(mdy, mx, mdys, mxs, dw, s);
+    conv1d_wgrad_sw128_kernel<<<grid, kWgThreads, smem, st>>>(mdy, mx, mdys, mxs, dw, s);
     CS_CUDA_OK(cudaGetLastError());
+    return CS_OK;
+}
+
+// What the dispatch would do for a shape, without launching anything (diagnostics and CPU-side tests).
+// direction: 0 forward, 1 data gradient from the forward weights, 2 weight gradient.  out[16]:
+//   forward / dgrad: {variant (0 plane kernel, 1 swizzled rows, 2 CTA pairs), NT, MT, AS, WS, slot, tma_store, smem bytes,
+//                     grid x, y, z, TMEM columns per CTA, tiles, units, 0, 0}
+//   weight gradient: {variant (0 plane kernel, 1 swizzled rows), NC, taps per CTA, tap groups, splits, slot, 0, smem bytes,
+//                     grid x, y, z, 512, tiles, 0, 0, 0}
+int conv1d_plan(int B, int L, int Cin, int Cout, int K, int pad, int direction, int* out) {
+    CS_REQUIRE(out != nullptr && direction >= 0 && direction <= 2, "conv1d_plan: bad arguments");
+    CS_REQUIRE(K >= 1 && K <= 64 && pad >= 0 && pad < K && B >= 1 && L >= 1, "conv1d_plan: bad shape");
+    for (int i = 0; i < 16; ++i) out[i] = 0;
+    const int Lout = L + 2 * pad - K + 1;
+    CS_REQUIRE(Lout >= 1, "conv1d_plan: empty output");
+    size_t smem = 0;
+    dim3 grid;
+    if (direction == 2) {
+        Wg128Shape s;
+        int passes = 0;
+        if (plan_wgrad128(B, L, Cin, Cout, K, pad, Lout, s, passes, smem, grid) != 0) return CS_OK;
+        const int v[16] = {1, s.NC, s.TP, passes, s.S, s.slot, 0, (int)smem, (int)grid.x, (int)grid.y, (int)grid.z, 512, s.total_tiles, 0, 0, 0};
+        memcpy(out, v, sizeof(v));
+        return CS_OK;
+    }
+    Fwd128Shape s;
+    int pair = 0, units = 0;
+    // the data gradient is the forward kernel on dy: reduction over Cout, outputs Cin, padding K-1-pad, output length L
+    const int rc = direction == 0 ? plan_fwd128(B, L, Cin, Cout, K, pad, Lout, 0, s, pair, smem, grid, units)
+                                  : plan_fwd128(B, Lout, Cout, Cin, K, K - 1 - pad, L, 1, s, pair, smem, grid, units);
+    if (rc != 0) return CS_OK;
+    int cols = 32;
+    while (cols < s.NT * s.MT) cols <<= 1;
+    const int v[16] = {pair ? 2 : 1, s.NT, s.MT, s.AS, s.WS, s.slot, s.tma_store, (int)smem, (int)grid.x, (int)grid.y, (int)grid.z, cols,
+                       s.total, units, 0, 0};
+    memcpy(out, v, sizeof(v));
     return CS_OK;
 }
 

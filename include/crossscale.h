@@ -141,6 +141,13 @@ int cs_conv1d_fwd_bn(const void* x, const void* w, const float* bias, void* y, i
                      float* mean, float* rstd, float* running_mean, float* running_var, float eps,
                      float momentum, const float* gamma, const float* beta, float* coef,
                      cs_stream_t stream);
+/* Which kernel variant and tile configuration the dispatch would use for a shape; launches nothing and needs no
+ * GPU (SM count defaults to 148 without one).  direction: 0 forward, 1 data gradient, 2 weight gradient.
+ * out16 (forward / data gradient): {variant: 0 plane kernel | 1 swizzled rows | 2 cta_group::2 pairs, NT, MT,
+ * activation stages, weight stages, slot, tma_store, shared-memory bytes, grid x, y, z, TMEM columns per CTA,
+ * tiles, units, 0, 0}; (weight gradient): {variant 0 | 1, NC, taps per CTA, tap groups, splits, slot, 0,
+ * shared-memory bytes, grid x, y, z, 512, tiles, 0, 0, 0}. */
+int cs_conv1d_plan(int B, int L, int Cin, int Cout, int K, int pad, int direction, int* out16);
 /* dx = conv_transpose(dy, w):  dy [B,Lout,Cout] bf16 -> dx [B,L,Cin] bf16.  wt is the
  * tap-flipped, channel-transposed weight [K, Cin, Cout] (cs_conv1d_prepare_dgrad_weight). */
 int cs_conv1d_dgrad(const void* dy, const void* wt, void* dx, int B, int L, int Cin, int Cout,
