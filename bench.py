@@ -180,9 +180,10 @@ def run_ours(args):
                    "gap_ms": round(gap, 4), "h2d_copy_ms": round(copy_ms, 4),
                    "host_enqueue_ms": round(mean([t["host_enqueue_ms"] for t in tr_]), 4),
                    "host_total_ms": round(mean([t["host_total_ms"] for t in tr_]), 4)}
-            for r_ in sorted(launch.gather_rows([row]), key=lambda r: r["rank"]):
-                sys.stderr.write("[e2e trace] " + json.dumps(r_) + "\n")
-            sys.stderr.flush()
+            rows_ = sorted(launch.gather_rows([row]), key=lambda r: r["rank"])
+            if rank == 0:                                    # one line, one writer: nothing to interleave with
+                sys.stderr.write("[e2e trace] " + json.dumps(rows_) + "\n")
+                sys.stderr.flush()
         e2e = {"value": samples / (e2e_ms / 1e3), "unit": "samples/s",
                "h2d_bytes_per_step": int(runner._stager.h2d_bytes), "d2h_bytes_per_step": int(runner.d2h_bytes),
                "ms_per_step": e2e_ms / K, "device_ms_per_step": e2e_dev_ms / K, "wall_ms_per_step": wall_ms / K, "stage_dtype": str(dt).replace("torch.", ""), "last_loss": last,

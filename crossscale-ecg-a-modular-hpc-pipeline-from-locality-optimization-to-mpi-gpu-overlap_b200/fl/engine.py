@@ -496,10 +496,13 @@ class FedAvgRunner:
                     g._cs_captured = True
                 g.replay()
                 tr.launches += self.local_steps
-        self._stager.release(slot)
         if trace is not None:
             ev1.record()
         self.agg.aggregate(self.flat, self.prev, self.weight, self.mom)
+        # the slot is handed back AFTER the aggregation: the next block's H2D copy waits on this event, and a 13 MB DMA
+        # running under the aggregation kernel slows its system-scope flag traffic (traced: 0.05 ms per round at two
+        # GPUs, 0.16-0.21 ms at eight, against 0.012-0.018 ms when nothing else touches the memory system)
+        self._stager.release(slot)
         st = torch.cuda.current_stream(self.device)
         if trace is not None:
             ev2.record()
