@@ -1,4 +1,5 @@
-"""`python -m crossscale.cli.plot_all_results [--results-dir D --csv F --batch B]` — see ``cli/plots.py``."""
+"""`python -m crossscale.cli.plot_all_results [--results-dir D --csv F --batch B]` — see ``cli/plots.py``.
+Reference: ``Module_1/plot_all_results.py:1-129`` (merged A0-A4 CSV, amortised "effective" A4 throughput ``:56-58``)."""
 import sys
 
 from .plots import main as _main

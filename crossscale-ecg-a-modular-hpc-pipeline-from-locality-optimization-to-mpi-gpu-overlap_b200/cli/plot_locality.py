@@ -1,4 +1,5 @@
-"""`python -m crossscale.cli.plot_locality [--results-dir D --csv F --batch B]` — see ``cli/plots.py``."""
+"""`python -m crossscale.cli.plot_locality [--results-dir D --csv F --batch B]` — see ``cli/plots.py``.
+Reference: ``Module_1/plot_locality.py:7-73`` (throughput vs batch, stacked data/h2d/compute bars at ``--batch``)."""
 import sys
 
 from .plots import main as _main

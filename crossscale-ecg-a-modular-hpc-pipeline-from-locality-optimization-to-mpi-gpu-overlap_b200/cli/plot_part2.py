@@ -1,4 +1,5 @@
-"""`python -m crossscale.cli.plot_part2 [--results-dir D --csv F --batch B]` — see ``cli/plots.py``."""
+"""`python -m crossscale.cli.plot_part2 [--results-dir D --csv F --batch B]` — see ``cli/plots.py``.
+Reference: ``Module_2/plot_part2.py:1-17`` and the two figures of ``Module_2/benchmark_part_2.py:141-178``."""
 import sys
 
 from .plots import main as _main

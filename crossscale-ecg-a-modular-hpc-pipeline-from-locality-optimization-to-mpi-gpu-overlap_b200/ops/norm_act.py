@@ -1,7 +1,10 @@
 """Fused BatchNorm(+residual)(+ReLU), pooling (K4) on channels-last bf16 activations.
 
-CUDA path: two memory-bound kernels forward (per-channel statistics, then normalise + affine +
-residual + ReLU in one pass) and two backward; CPU path: stock PyTorch on ``[B, C, L]`` (oracle).
+No counterpart in the reference (its only model, ``Module_3/tiny_ecg_model.py:8-29``, has no normalisation layer); this
+is the "fused BN/ReLU/pool" of the north-star ResNet-1D config.  CUDA path: the training statistics come out of the
+producing convolution's epilogue (``conv_bn``) or one statistics kernel, then one pass does normalise + affine +
+residual + ReLU; backward is one reduction and one elementwise pass; all reductions finish inside their own kernel
+through a persistent per-layer workspace.  CPU path: stock PyTorch on ``[B, C, L]`` (oracle).
 """
 from __future__ import annotations
 

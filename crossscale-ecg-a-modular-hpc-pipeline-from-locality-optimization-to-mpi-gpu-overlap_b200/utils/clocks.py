@@ -1,4 +1,5 @@
-"""Sample ``nvidia-smi`` clocks and throttle reasons while a timed region runs."""
+"""Sample ``nvidia-smi`` clocks and throttle reasons while a timed region runs (bench contract; the reference records
+no clocks: its timing is ``time.perf_counter`` around ``cuda.synchronize``, ``Module_1/bench_locality.py:44-66``)."""
 from __future__ import annotations
 
 import shutil

@@ -1,4 +1,10 @@
-"""Seeds, device selection, checkpoints."""
+"""Seeds, device selection, checkpoints.
+
+Reference: ``set_basic_seeds`` ``Module_3/TRUE_FL_M3/part3_fedavg_overlap_mpi_gpu.py:66-70`` (seed ``1234 + rank``, ``:156``);
+``setup_device`` ``:60-63`` / ``Module_3/part3_mpi_gpu_train.py:82-86`` (there every rank lands on ``cuda:0``; here
+``cuda:LOCAL_RANK``).  The reference has no checkpointing; ``save/load_checkpoint`` store exactly the
+``state_dict`` of ``Module_3/tiny_ecg_model.py:8-29``.
+"""
 from __future__ import annotations
 
 import os

@@ -2,6 +2,9 @@
 // fused unscale / inf-check / scaler update (K6), z-score staging (K10), BN / ReLU / residual /
 // pooling (K4) and layout converters.  All are CUDA-core kernels sized against HBM bandwidth:
 // 128-bit accesses, grid-stride loops, one pass over the data where the math allows it.
+// Reference call sites they replace: x_gpu[sel] (Module_3/shard_dataset.py:135-136), F.cross_entropy + GradScaler
+// (Module_3/TRUE_FL_M3/part3_fedavg_overlap_mpi_gpu.py:121-127), torch.optim.SGD(lr=1e-2, momentum=0.9) (:181), the
+// per-window z-score of the LABL loader (Module_1/labl_loader(EXPERIMENTAL).py:65-69); BN / pooling have no counterpart.
 #include "common/cs_common.cuh"
 #include <stdlib.h>
 
