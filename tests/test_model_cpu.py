@@ -78,3 +78,34 @@ def test_checkpoint_round_trip(tmp_path):
 def test_tiny1d_alias_and_registry():
     assert isinstance(Tiny1D(), TinyECG) and Tiny1D(in_ch=1, num_classes=5).num_classes == 5
     assert isinstance(build_model("tiny_ecg", 2), TinyECG)
+
+
+def test_resnet1d_cpu_path_trains_and_matches_stock_layers():
+    """ResNet-1D on CPU goes through plain PyTorch (F.conv1d / F.batch_norm behind Conv1dB200 / BNReLU1d / conv_bn): the
+    oracle the CUDA kernels are tested against.  Parameter count of the wide model, tap-major weight views, one SGD step."""
+    import torch.nn.functional as F
+    from crossscale.models import build_model
+    from crossscale.models.resnet1d_wide import resnet1d_wide_25m
+    from crossscale.ops.conv1d import Conv1dB200
+    from crossscale.ops.norm_act import BNReLU1d, conv_bn
+
+    torch.manual_seed(0)
+    m = build_model("resnet1d_small", 5)
+    x, y = torch.randn(6, 1, 120), torch.randint(0, 5, (6,))
+    opt = torch.optim.SGD(m.parameters(), lr=0.05, momentum=0.9)
+    losses = []
+    for _ in range(8):
+        loss = F.cross_entropy(m(x), y)
+        opt.zero_grad(); loss.backward(); opt.step()
+        losses.append(float(loss))
+    assert losses[-1] < losses[0] and all(p.grad is not None for p in m.parameters())
+
+    conv, bn = Conv1dB200(8, 16, 5, padding=2, bias=False), BNReLU1d(16, relu=True)
+    xc, res = torch.randn(3, 8, 40), torch.randn(3, 16, 40)
+    ref = F.relu(F.batch_norm(F.conv1d(xc, conv.weight_oik, padding=2), None, None, bn.weight, bn.bias, True, 0.1, 1e-5) + res)
+    assert torch.allclose(conv_bn(conv, bn, xc, residual=res), ref, atol=1e-6)
+    assert tuple(conv.weight.shape) == (5, 16, 8) and tuple(conv.weight_oik.shape) == (16, 8, 5)
+
+    wide = resnet1d_wide_25m(5)
+    n = sum(p.numel() for p in wide.parameters())
+    assert 24_000_000 < n < 25_000_000                      # "~25 M parameters" stress config of BASELINE.json
