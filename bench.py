@@ -43,6 +43,8 @@ def parse():
     ap.add_argument("--num-windows", type=int, default=NUM_WINDOWS)
     ap.add_argument("--trace-e2e", action="store_true", help="per-rank timing breakdown of the staged rounds on stderr")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-arms", action="store_true", help="skip the extra fp16+scaler / fp32 arms measured after the headline")
+    ap.add_argument("--windows", type=int, default=5, help="timed windows of --steps rounds each (value = median)")
     return ap.parse_args()
 
 
@@ -64,6 +66,18 @@ def emit(obj):
 
 
 # ------------------------------------------------------------------------------------------------
+def _config(world, cfg, num_windows, K, W):
+    """The structured part of the record: identical keys AND values in both arms (prose goes to `notes`)."""
+    return {"model": f"TinyECG(num_classes={NUM_CLASSES})", "global_batch": BATCH * world, "seq_len": WIN_LEN,
+            "parallelism": f"fedavg{world} (1 client/GPU)", "local_steps": LOCAL_STEPS, "batch_per_client": BATCH,
+            "fl_config": cfg, "windows_per_client": num_windows, "rounds_timed": K, "warmup_rounds": W}
+
+
+def _median(v):
+    v = sorted(v)
+    return v[len(v) // 2] if len(v) % 2 else 0.5 * (v[len(v) // 2 - 1] + v[len(v) // 2])
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -83,16 +97,11 @@ def run_ours(args):
         return
     device = setup_device(local_rank)
     set_basic_seeds(1234 + rank)
-    K, W = args.steps, max(args.warmup, 3)
+    K, W, R = args.steps, max(args.warmup, 3), max(args.windows, 1)
     tmp = tempfile.mkdtemp(prefix="cs_bench_")
     shard_dir = make_shards(tmp, rank, args.num_windows)
     paths = sorted(glob(os.path.join(shard_dir, "ecg_*.bin")))
     x_gpu, y_gpu = load_shards_to_gpu(paths, device=device, max_windows=args.num_windows)
-
-    model = TinyECG(num_classes=NUM_CLASSES).to(device)
-    cfg = "G0" if args.amp == "none" else "G1"
-    runner = FedAvgRunner(model, device, x_gpu, y_gpu, BATCH, LOCAL_STEPS, cfg, amp=args.amp, rank=rank,
-                          world=world, agg_backend=args.agg_backend)
 
     def sync_all():
         torch.cuda.synchronize()
@@ -100,11 +109,38 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    # ---- device-timed rounds (GPU-resident data, like the reference) ----------------------------
-    # one nvidia-smi poller for the job (rank 0's GPU; eight of them contend for the driver with the launching threads).
-    # It is started BEFORE the pre-heat and given time to deliver its first sample: nvidia-smi's start-up (NVML init,
-    # driver queries) can stall kernel launches for milliseconds, which is a large share of a 16 ms timed region
-    # (seen as occasional 0.99-1.04 ms rounds instead of 0.81-0.83 when it was started right before the timed loop).
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+
+    def timed_windows(fn, n_windows):
+        """n_windows x (exactly K calls of fn), each bracketed by barrier + synchronize; device time, max over ranks"""
+        out = []
+        for _ in range(n_windows):
+            sync_all()
+            e0.record()
+            for _ in range(K):
+                fn()
+            e1.record()
+            sync_all()
+            out.append(max_over_ranks(e0.elapsed_time(e1), device))
+        return out
+
+    def make_runner(amp):
+        model = TinyECG(num_classes=NUM_CLASSES).to(device)
+        cfg = "G0" if amp == "none" else "G1"
+        return FedAvgRunner(model, device, x_gpu, y_gpu, BATCH, LOCAL_STEPS, cfg, amp=amp, rank=rank, world=world,
+                            agg_backend=args.agg_backend), cfg
+
+    def preheat(runner, n):
+        # a fixed COUNT, not a wall-clock loop: every rank must run the same number of aggregation rounds
+        for i in range(n):
+            runner.run_round_async()
+            if i % 16 == 15:
+                torch.cuda.synchronize()
+
+    runner, cfg = make_runner(args.amp)
+
+    # one nvidia-smi poller for the job (rank 0's GPU), started BEFORE the pre-heat and given time to deliver its first
+    # sample: its start-up (NVML init, driver queries) can stall kernel launches for milliseconds
     sampler = ClockSampler(gpu_index=torch.cuda.current_device())
     if rank == 0:
         sampler.start()
@@ -112,38 +148,52 @@ def run_ours(args):
         while sampler.proc is not None and not sampler.lines and time.perf_counter() - t_wait < 2.0:
             time.sleep(0.01)
     sync_all()
-    # pre-heat: a GPU that sat idle while Python started takes tens of ms to reach its boost clocks, longer than the
-    # W warm-up rounds (W * 0.8 ms); spin ~0.25 s of untimed rounds first so the timed rounds see steady clocks
-    # (a fixed COUNT, not a wall-clock loop: every rank must run the same number of aggregation rounds)
-    for i in range(PREHEAT_ROUNDS):
-        runner.run_round_async()
-        if i % 16 == 15:
-            torch.cuda.synchronize()
+    preheat(runner, PREHEAT_ROUNDS)          # clock ramp from idle takes longer than W warm-up rounds
     for _ in range(W):
         runner.run_round_async()
     sync_all()
+
+    # ---- device-timed rounds (GPU-resident data, like the reference): R windows of exactly K rounds ----------------
     launches0 = runner.trainer.launches + runner.agg.launches
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(K):
-        runner.run_round_async()
-    e1.record()
-    sync_all()
-    dev_ms = max_over_ranks(e0.elapsed_time(e1), device)
-    launches = runner.trainer.launches + runner.agg.launches - launches0
-    # aggregation alone (exposed: nothing overlaps it), device-timed
-    a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    sync_all()
-    a0.record()
-    for _ in range(K):
-        runner.agg.aggregate(runner.flat, runner.prev, runner.weight, runner.mom)
-    a1.record()
-    sync_all()
-    agg_ms = max_over_ranks(a0.elapsed_time(a1), device) / K
+    win_ms = timed_windows(runner.run_round_async, R)
+    launches = (runner.trainer.launches + runner.agg.launches - launches0) // R
+    dev_ms = _median(win_ms)
+    runner.check_health()
+    # the same rounds without the aggregation: exposed aggregation = round - no-communication round
+    nocomm_ms = timed_windows(lambda: runner.run_round_async(aggregate=False), max(3, R // 2 + 1))
+    exposed_ms = max(0.0, (dev_ms - _median(nocomm_ms)) / K)
+    # ... and the stand-alone aggregation kernel back to back (its launch + barrier latency, nothing overlapping)
+    agg_alone = timed_windows(lambda: runner.agg.aggregate(runner.flat, runner.prev, runner.weight, runner.mom), 1)[0] / K
     loss_dev = runner.trainer.state.loss_sum()
+    rounds_run = runner.trainer.state.steps_done() // LOCAL_STEPS
 
     samples = world * K * LOCAL_STEPS * BATCH
     value = samples / (dev_ms / 1e3)
+
+    # ---- multi-GPU correctness, outside the timed region -----------------------------------------------------------
+    replicas_identical, agg_err = None, None
+    if world > 1:
+        flat = runner.flat.detach()
+        n = runner.numel
+        words = flat[:n].contiguous().view(torch.int32).to(torch.int64)
+        h = torch.stack([words.sum(), (words * torch.arange(1, n + 1, device=device)).sum()])
+        hs = [torch.zeros_like(h) for _ in range(world)]
+        dist.all_gather(hs, h)
+        replicas_identical = bool(all(torch.equal(hs[0], t) for t in hs))
+        # one extra aggregation with UNEQUAL weights against the fp64 oracle sum_i w_i theta_i
+        g = torch.Generator(device=device).manual_seed(99 + rank)
+        prev_t = runner.prev.clone()
+        loc_t = prev_t + 0.01 * torch.randn(prev_t.shape, device=device, generator=g)
+        w_r = (rank + 1) / (world * (world + 1) / 2)
+        locs = [torch.zeros_like(loc_t) for _ in range(world)]
+        dist.all_gather(locs, loc_t)
+        want = prev_t[:n].double() + sum(((r + 1) / (world * (world + 1) / 2)) * (locs[r][:n].double() - prev_t[:n].double())
+                                         for r in range(world))
+        runner.agg.aggregate(loc_t, prev_t, w_r, None)
+        torch.cuda.synchronize()
+        err = torch.tensor([float((loc_t[:n].double() - want).abs().max())], device=device, dtype=torch.float64)
+        dist.all_reduce(err, op=dist.ReduceOp.MAX)
+        agg_err = float(err.item())
 
     # ---- end-to-end rounds: pinned host -> H2D every round, loss D2H every round -------------------
     e2e = None
@@ -151,23 +201,27 @@ def run_ours(args):
         dt = torch.bfloat16 if args.amp == "bf16" else torch.float32
         store = PinnedShardStore(paths, max_windows=args.num_windows, dtype=dt)
         runner.enable_e2e(store, seed=rank)
-        for _ in range(max(W, 4)):                           # 2 eager rounds + 2 graph captures (one per staging slot)
+        for _ in range(max(W, 4)):
             runner.run_round_e2e(pipelined=True)
         runner.drain_e2e()
         if args.trace_e2e:
             runner.e2e_trace, runner._stager.trace = [], []
-        sync_all()
-        t0 = time.perf_counter()
-        e0.record()
-        last = 0.0
-        for _ in range(K):
-            last = runner.run_round_e2e(pipelined=True)      # reads the previous round's loss while this one runs
-        last = runner.drain_e2e()                            # ... and the last round's loss, still inside the timed region
-        e1.record()
-        sync_all()
-        wall_ms = (time.perf_counter() - t0) * 1e3
-        e2e_dev_ms = e0.elapsed_time(e1)
-        e2e_ms = max_over_ranks(max(e2e_dev_ms, wall_ms), device)
+        e2e_win, e2e_dev_win, e2e_wall_win, last = [], [], [], 0.0
+        for _ in range(R):
+            sync_all()
+            t0 = time.perf_counter()
+            e0.record()
+            for _ in range(K):
+                last = runner.run_round_e2e(pipelined=True)      # reads an earlier round's loss while this one runs
+            last = runner.drain_e2e()                            # ... and the last rounds' losses, inside the timed region
+            e1.record()
+            sync_all()
+            wall = (time.perf_counter() - t0) * 1e3
+            devt = e0.elapsed_time(e1)
+            e2e_wall_win.append(wall)
+            e2e_dev_win.append(devt)
+            e2e_win.append(max_over_ranks(max(devt, wall), device))
+        e2e_ms = _median(e2e_win)
         if args.trace_e2e:                                   # per-rank diagnostics of the staged rounds (stderr)
             tr_, cp_ = runner.e2e_trace, runner._stager.trace
             mean = lambda v: sum(v) / max(1, len(v))
@@ -181,16 +235,39 @@ def run_ours(args):
                    "host_enqueue_ms": round(mean([t["host_enqueue_ms"] for t in tr_]), 4),
                    "host_total_ms": round(mean([t["host_total_ms"] for t in tr_]), 4)}
             rows_ = sorted(launch.gather_rows([row]), key=lambda r: r["rank"])
-            if rank == 0:                                    # one line, one writer: nothing to interleave with
+            if rank == 0:
                 sys.stderr.write("[e2e trace] " + json.dumps(rows_) + "\n")
                 sys.stderr.flush()
         e2e = {"value": samples / (e2e_ms / 1e3), "unit": "samples/s",
                "h2d_bytes_per_step": int(runner._stager.h2d_bytes), "d2h_bytes_per_step": int(runner.d2h_bytes),
-               "ms_per_step": e2e_ms / K, "device_ms_per_step": e2e_dev_ms / K, "wall_ms_per_step": wall_ms / K, "stage_dtype": str(dt).replace("torch.", ""), "last_loss": last,
+               "ms_per_step": e2e_ms / K, "windows_ms_per_step": [round(t / K, 5) for t in e2e_win],
+               "device_ms_per_step": _median(e2e_dev_win) / K, "wall_ms_per_step": _median(e2e_wall_win) / K,
+               "stage_dtype": str(dt).replace("torch.", ""), "last_loss": last,
+               "sampler": "contiguous blocks of 12800 windows from the pinned store, block order reshuffled per epoch",
                "loss_readback": "every round's loss is copied device->host and read by the host in order, up to two rounds "
                                 "behind the enqueue (drained inside the timed region)"}
-    clocks = sampler.stop()
     status = runner.agg.comm.status() if getattr(runner.agg, "comm", None) is not None else 0
+    fused = bool(getattr(runner, "fuse_agg", False))
+    backend = runner.agg.backend
+    runner.close()
+
+    # ---- like-for-like arms in the same job: fp16 + GradScaler (the reference's G1) and fp32 (its G0) ------------
+    arms = {}
+    if not args.no_arms:
+        for amp in ("fp16", "none", "bf16"):
+            if amp == args.amp:
+                continue
+            r2, cfg2 = make_runner(amp)
+            preheat(r2, 48)
+            ms2 = timed_windows(r2.run_round_async, 3)
+            r2.check_health()
+            arms[{"fp16": "fp16_scaler", "none": "fp32", "bf16": "bf16"}[amp]] = {
+                "fl_config": cfg2, "value": samples / (_median(ms2) / 1e3), "ms_per_step": _median(ms2) / K,
+                "windows_ms_per_step": [round(t / K, 5) for t in ms2],
+                "loss_scale": r2.trainer.state.loss_scale(), "skipped_steps": r2.trainer.state.skipped_steps(),
+                "one_launch_per_round": bool(r2.trainer.use_round)}
+            r2.close()
+    clocks = sampler.stop()
 
     if rank == 0:
         base = None
@@ -206,20 +283,33 @@ def run_ours(args):
             "vs_baseline": (value / base) if base else None,
             "dtype": {"bf16": "bf16", "fp16": "fp16", "none": "fp32"}[args.amp], "data": "synthetic",
             "impl": "ours",
-            "config": {"model": "TinyECG(num_classes=2)", "global_batch": BATCH * world, "seq_len": WIN_LEN,
-                       "parallelism": f"fedavg{world} (1 client/GPU)", "local_steps": LOCAL_STEPS,
-                       "batch_per_client": BATCH, "fl_config": cfg, "step": "one FL round = 50 local steps + aggregation",
-                       "windows_per_client": args.num_windows,
-                       "l2": "inputs larger than L2 (262 MB resident dataset per client, random gather)",
-                       "aggregation": runner.agg.backend,
-                       "preheat": f"{PREHEAT_ROUNDS} untimed rounds (~0.25 s) before the {W} warm-up rounds (clock ramp from idle)"},
-            "exposed_agg_ms_per_round": agg_ms, "avg_loss": loss_dev / max(1, (W + K) * LOCAL_STEPS),
+            "config": _config(world, cfg, args.num_windows, K, W),
+            "windows_ms_per_step": [round(t / K, 5) for t in win_ms],
+            "ms_per_step_min": min(win_ms) / K, "ms_per_step_max": max(win_ms) / K,
+            "exposed_agg_ms_per_round": exposed_ms, "agg_alone_ms_per_round": agg_alone,
+            "no_comm_ms_per_step": _median(nocomm_ms) / K,
+            "avg_loss": loss_dev / max(1, rounds_run * LOCAL_STEPS),
             "clocks": clocks, "gpu_launches": int(launches), "comm_status": status,
+            "notes": {
+                "step": "one FL round = 50 local steps + FedAvg aggregation"
+                        + (" in ONE cooperative kernel launch (persistent round kernel, aggregation push in its tail)" if fused else ""),
+                "value": f"median of {R} windows of exactly {K} rounds; each window bracketed by barrier + cuda synchronize, "
+                         "CUDA events on the launching stream, max over ranks",
+                "l2": "inputs larger than L2 (262 MB resident dataset per client, random gather)",
+                "sampler_resident": "per-epoch permutation of the client's windows, generated in-kernel (counter-based bijection), "
+                                    "ragged tail dropped" if fused else "per-epoch torch.randperm, ragged tail dropped",
+                "aggregation": backend,
+                "exposed_agg": "median round with aggregation minus median round without (same kernel, comm=NULL)",
+                "preheat": f"{PREHEAT_ROUNDS} untimed rounds before the {W} warm-up rounds (clock ramp from idle)"},
         }
+        if replicas_identical is not None:
+            out["replicas_identical"] = replicas_identical
+            out["agg_max_abs_err"] = agg_err
+        if arms:
+            out["arms"] = arms
         if e2e is not None:
             out["e2e"] = e2e
         emit(out)
-    runner.close()
     launch.shutdown()
 
 
@@ -247,6 +337,7 @@ def run_reference(args):
     sys.path.insert(0, os.path.join(REPO, "baseline", "mpi_shim"))   # mpi4py is not in the image
     sys.path.insert(0, script_dir)
     K, W = args.steps, max(args.warmup, 3)
+    ref_cfg = "G0" if args.amp == "none" else "G1"          # the reference's own --config: G0 = fp32, G1 = fp16 autocast + GradScaler
     # one directory for the whole job: every rank is a child of the same torchrun agent
     tmp = (tempfile.mkdtemp(prefix="cs_bench_ref_") if world == 1
            else os.path.join(tempfile.gettempdir(), f"cs_bench_ref_{os.getppid()}"))
@@ -270,7 +361,7 @@ def run_reference(args):
     from crossscale.utils.clocks import ClockSampler
     sampler = ClockSampler(gpu_index=int(os.environ.get("LOCAL_RANK", "0"))).start()
     argv = [script, "--data-root", shard_dir, "--batch-size", str(BATCH), "--rounds", str(W + K),
-            "--local-steps", str(LOCAL_STEPS), "--max-windows", str(args.num_windows), "--config", "G1"]
+            "--local-steps", str(LOCAL_STEPS), "--max-windows", str(args.num_windows), "--config", ref_cfg]
     old = sys.argv
     sys.argv = argv
     try:
@@ -284,7 +375,7 @@ def run_reference(args):
         return
     import csv as _csv
     with open(csv) as f:
-        rows = [r for r in _csv.DictReader(f) if r["config"] == "G1" and int(r["round_idx"]) >= W]
+        rows = [r for r in _csv.DictReader(f) if r["config"] == ref_cfg and int(r["round_idx"]) >= W]
     per_rank = {}
     for r in rows:
         per_rank.setdefault(int(r["rank"]), []).append(float(r["local_train_ms"]) + float(r["comm_ms"]))
@@ -294,15 +385,13 @@ def run_reference(args):
     value = samples / (total_ms / 1e3)
     emit({"metric": METRIC, "value": value, "unit": "samples/s", "n_gpus": world, "steps": K, "warmup": W,
           "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-          "dtype": "fp16", "data": "synthetic", "impl": "reference",
-          "config": {"model": "TinyECG(num_classes=2)", "global_batch": BATCH * world, "seq_len": WIN_LEN,
-                     "parallelism": f"fedavg{world} (1 client/GPU)", "local_steps": LOCAL_STEPS,
-                     "batch_per_client": BATCH, "fl_config": "G1 (torch.cuda.amp.autocast fp16 + GradScaler)",
-                     "step": "one FL round = 50 local steps + Bcast + Allreduce",
-                     "windows_per_client": args.num_windows,
-                     "timing": "reference's own perf_counter brackets (every step ends in cuda.synchronize), "
-                               "local_train_ms + comm_ms summed over timed rounds, max over ranks",
-                     "mpi": "mpi4py shim over torch.distributed gloo (host buffers), torchrun launch"},
+          "dtype": "fp32" if ref_cfg == "G0" else "fp16", "data": "synthetic", "impl": "reference",
+          "config": _config(world, ref_cfg, args.num_windows, K, W),
+          "notes": {"step": "one FL round = 50 local steps + Bcast + Allreduce",
+                    "fl_config": "G0 fp32" if ref_cfg == "G0" else "G1 (torch.cuda.amp.autocast fp16 + GradScaler)",
+                    "timing": "reference's own perf_counter brackets (every step ends in cuda.synchronize), "
+                              "local_train_ms + comm_ms summed over timed rounds, max over ranks",
+                    "mpi": "mpi4py shim over torch.distributed gloo (host buffers), torchrun launch"},
           "exposed_agg_ms_per_round": comm_ms, "clocks": clocks,
           "e2e": {"value": value, "unit": "samples/s", "h2d_bytes_per_step": 0,
                   "d2h_bytes_per_step": 4 * LOCAL_STEPS + 2 * 5832,

@@ -72,6 +72,8 @@ class ShardDataset(Dataset):
         else:
             self.y = torch.zeros(arr.shape[0], dtype=torch.long)
         self.has_labels = bool(have_labels and ys)
+        if self.y.shape[0] != self.x.shape[0]:
+            raise RuntimeError(f"labels ({self.y.shape[0]}) and windows ({self.x.shape[0]}) disagree")
 
     def __len__(self) -> int:
         return self.x.shape[0]

@@ -68,6 +68,12 @@ def write_shard(path: str, windows: np.ndarray, labels: Optional[np.ndarray] = N
             f.write(_HDR.pack(n, nc))
             f.write(lab.tobytes())
         os.replace(ltmp, label_path_for(path))
+    else:
+        # an unlabelled shard must not inherit the sidecar of whatever was written under this name before
+        try:
+            os.unlink(label_path_for(path))
+        except FileNotFoundError:
+            pass
     return ShardHeader(n, l)
 
 
@@ -108,4 +114,10 @@ def load_labels(path: str) -> Optional[Tuple[np.ndarray, int]]:
         lab = np.frombuffer(f.read(n), dtype=np.uint8)
     if lab.size != n:
         raise RuntimeError(f"label sidecar {lp}: truncated")
+    shard_n = read_header(path).num_windows
+    if n != shard_n:
+        # a sidecar left behind by an earlier data set of a different size: labels that belong to other windows
+        import warnings
+        warnings.warn(f"label sidecar {lp} holds {n} labels but shard {path} has {shard_n} windows; ignoring the sidecar")
+        return None
     return lab.astype(np.int64), int(nc)

@@ -223,20 +223,35 @@ class KernelLocalTrainer:
 
 
 class FusedTinyTrainer:
-    """TinyECG local training with the one-launch step kernel + CUDA-graph replay."""
+    """TinyECG local training on the fused kernels.
+
+    G1 (bf16 / fp16): the persistent round kernel - ``local_steps`` steps (and, when the caller passes
+    ``fused_agg``, the FedAvg aggregation) are ONE cooperative launch; batches come from the kernel's own
+    per-epoch permutation, so no ``randperm`` / index copy is on the stream.  G0 (fp32) and ``use_round=False``:
+    one launch per step, a round's launches captured once in a CUDA graph."""
 
     def __init__(self, model: TinyECG, x_gpu: torch.Tensor, y_gpu: torch.Tensor, batch: int,
                  local_steps: int, lr=1e-2, momentum=0.9, amp: str = "none", use_graph: bool = True,
-                 generator: Optional[torch.Generator] = None):
+                 generator: Optional[torch.Generator] = None, use_round: Optional[bool] = None,
+                 check_labels: bool = True):
+        import os
         assert x_gpu.is_cuda and x_gpu.dim() == 2
         self.model, self.batch, self.local_steps = model, batch, local_steps
+        if check_labels:
+            tk.validate_labels(y_gpu, model.num_classes)        # one sync at set-up; the kernels only flag, never fault
         self.flat = model.flatten_parameters()
         amp_code = tk.AMP_BY_NAME[amp]
         self.state = tk.TinyTrainState(self.flat.flat, model.num_classes, lr=lr, momentum=momentum,
                                        amp=amp_code, scaler=tk.ScalerConfig(enabled=(amp == "fp16")))
         self.x, self.y = x_gpu, y_gpu
-        self.stream_idx = IndexStream(x_gpu.shape[0], batch, x_gpu.device, generator)
-        self.idx = torch.zeros(local_steps * batch, dtype=torch.int64, device=x_gpu.device)
+        if x_gpu.shape[0] < batch:
+            raise ValueError(f"dataset has {x_gpu.shape[0]} windows < batch {batch}")
+        if use_round is None:
+            use_round = os.environ.get("CROSSSCALE_TINY_ROUND", "1") != "0"
+        self.use_round = bool(use_round) and self.state.round_supported() and tk.round_kernel_available()
+        self.seed = int(generator.initial_seed() if generator is not None else torch.initial_seed()) & ((1 << 63) - 1)
+        self.stream_idx = None if self.use_round else IndexStream(x_gpu.shape[0], batch, x_gpu.device, generator)
+        self.idx = None if self.use_round else torch.zeros(local_steps * batch, dtype=torch.int64, device=x_gpu.device)
         self.use_graph, self.graph, self._warm = use_graph, None, False
         self.launches = 0
 
@@ -245,8 +260,15 @@ class FusedTinyTrainer:
         for s in range(self.local_steps):
             self.state.step(self.x, self.y, self.idx[s * b:(s + 1) * b], batch=b)
 
-    def run_round_resident(self) -> None:
-        """``local_steps`` fused steps over the GPU-resident dataset (asynchronous)."""
+    def run_round_resident(self, fused_agg: Optional[dict] = None) -> None:
+        """``local_steps`` fused steps over the GPU-resident dataset (asynchronous).  ``fused_agg``: keyword
+        arguments of :meth:`TinyTrainState.round` that make the launch end in the FedAvg aggregation."""
+        if self.use_round:
+            self.state.round(self.x, self.y, self.local_steps, self.batch, sample_mode=tk.SAMPLE_PERM, seed=self.seed,
+                             **(fused_agg or {}))
+            self.launches += 1
+            return
+        assert fused_agg is None
         self.stream_idx.fill(self.idx)
         if not self.use_graph or not self._warm:
             self._resident_steps()                 # first round runs eagerly (one-time kernel set-up)
@@ -259,9 +281,14 @@ class FusedTinyTrainer:
             self.graph.replay()
         self.launches += self.local_steps
 
-    def run_round_staged(self, xb: torch.Tensor, yb: torch.Tensor) -> None:
+    def run_round_staged(self, xb: torch.Tensor, yb: torch.Tensor, fused_agg: Optional[dict] = None) -> None:
         """``local_steps`` fused steps over a staged device buffer ``[steps*B, L]`` (fp32 or bf16)."""
         b = self.batch
+        if self.use_round:
+            self.state.round(xb, yb, self.local_steps, b, sample_mode=tk.SAMPLE_ROWS, **(fused_agg or {}))
+            self.launches += 1
+            return
+        assert fused_agg is None
         for s in range(self.local_steps):
             self.state.step(xb[s * b:(s + 1) * b], yb[s * b:(s + 1) * b], None, batch=b)
         self.launches += self.local_steps
@@ -289,8 +316,8 @@ def _run_pseudo(model, batch_iter, device, steps, rank, batch_size, world, amp, 
         # the steps run as replays of one CUDA graph of `chunk` fused steps (steps is rounded up to whole chunks)
         chunk = min(steps, 50)
         tr = FusedTinyTrainer(model, x_gpu, y_gpu, batch_size, chunk, amp=amp)
-        tr.run_round_resident()                       # eager warm-up
-        tr.run_round_resident()                       # graph capture + first replay
+        tr.run_round_resident()                       # warm-up (eager steps on the graph path)
+        tr.run_round_resident()                       # graph capture + first replay on the graph path
         torch.cuda.synchronize()
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record()
@@ -302,6 +329,7 @@ def _run_pseudo(model, batch_iter, device, steps, rank, batch_size, world, amp, 
                 print(f"[{label}] step {done}/{steps}", flush=True)
         b.record()
         torch.cuda.synchronize()
+        tr.state.check_errors()
         return _bench_row(label, world, rank, batch_size, done, 0.0, 0.0, a.elapsed_time(b))
     tr = TorchLocalTrainer(model, device, amp=amp)
     t0 = time.perf_counter()
@@ -381,6 +409,23 @@ class FedAvgRunner:
             self.agg.set_weights(self.weight)
         self.prev = self.flat.clone()
         self.rows: List[dict] = []
+        # TinyECG on the persistent round kernel: the aggregation rides in the tail of the same launch
+        self.fuse_agg = (self.fused and self.trainer.use_round and self.agg.backend == "kernel" and not self.agg.inplace
+                         and self.numel <= 4096)
+
+    def _fused_agg_args(self) -> dict:
+        a = self.agg
+        return dict(comm=a.comm.handle, prev=self.prev, weight=self.weight, wire_bf16=bool(a.wire_bf16),
+                    server_lr=a.server_lr, reset_momentum=a.reset_momentum, arena_off=0, channel=a.channel)
+
+    def check_health(self) -> None:
+        """Raise if a device-side time-out or error was flagged (call after a synchronisation point)."""
+        comm = getattr(self.agg, "comm", None)
+        if comm is not None and self.agg.backend == "kernel" and comm.status() != 0:
+            raise RuntimeError("FedAvg aggregation: a peer did not reach the cross-GPU barrier in time; the affected "
+                               "blocks kept their local parameters (replicas may differ) - aborting instead of training on")
+        if self.fused:
+            self.trainer.state.check_errors()
 
     def _events(self):
         return [torch.cuda.Event(enable_timing=True) for _ in range(3)]
@@ -394,6 +439,8 @@ class FedAvgRunner:
         t0 = time.perf_counter()
         if self.fused:
             self.trainer.state.reset_loss()
+            # (timed rounds keep local training and aggregation as two launches so that both columns of the
+            # reference's CSV - local_train_ms, comm_ms - are measured; run_round_async fuses them)
             self.trainer.run_round_resident()
         else:
             loss_acc, n_samples = self.trainer.run_steps(self.batch_iter, self.local_steps)
@@ -407,6 +454,7 @@ class FedAvgRunner:
         if cuda:
             e2.record()
             torch.cuda.synchronize()
+            self.check_health()
             local_ms, comm_ms = e0.elapsed_time(e1), e1.elapsed_time(e2)
         else:
             t2 = time.perf_counter()
@@ -428,10 +476,17 @@ class FedAvgRunner:
         return self.rows
 
     # -- asynchronous round (device-timed benchmarks): nothing here synchronises the host -------
-    def run_round_async(self) -> None:
+    def run_round_async(self, aggregate: bool = True) -> None:
+        """One round, enqueued only.  On the persistent-kernel path local steps AND aggregation are one launch;
+        ``aggregate=False`` runs the local steps alone (the no-communication round of the exposed-time measurement)."""
         assert self.fused, "async rounds need the fused CUDA trainer"
+        if self.fuse_agg:
+            self.trainer.run_round_resident(self._fused_agg_args() if aggregate else None)
+            self.agg.launches += 0
+            return
         self.trainer.run_round_resident()
-        self.agg.aggregate(self.flat, self.prev, self.weight, self.mom)
+        if aggregate:
+            self.agg.aggregate(self.flat, self.prev, self.weight, self.mom)
 
     # -- end-to-end round: pinned-host block -> H2D on the copy stream -> train -> aggregate ->
     #    loss read back to the host (the call a user makes when data does not live on the GPU) ---
@@ -481,7 +536,10 @@ class FedAvgRunner:
         if trace is not None:
             ev0, ev1, ev2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
             ev0.record()
-        if not tr.use_graph:
+        fused_here = self.fuse_agg
+        if tr.use_round:
+            tr.run_round_staged(xb, yb, self._fused_agg_args() if fused_here else None)
+        elif not tr.use_graph:
             tr.run_round_staged(xb, yb)
         else:
             if self._graphs[slot] is None:
@@ -498,7 +556,8 @@ class FedAvgRunner:
                 tr.launches += self.local_steps
         if trace is not None:
             ev1.record()
-        self.agg.aggregate(self.flat, self.prev, self.weight, self.mom)
+        if not fused_here:
+            self.agg.aggregate(self.flat, self.prev, self.weight, self.mom)
         # the slot is handed back AFTER the aggregation: the next block's H2D copy waits on this event, and a 13 MB DMA
         # running under the aggregation kernel slows its system-scope flag traffic (traced: 0.05 ms per round at two
         # GPUs, 0.16-0.21 ms at eight, against 0.012-0.018 ms when nothing else touches the memory system)
@@ -534,8 +593,10 @@ class FedAvgRunner:
         return self._last_loss
 
     def drain_e2e(self) -> float:
-        """Read the losses of the rounds still in flight (pipelined mode)."""
-        return self._collect_losses(self._e2e_rounds)
+        """Read the losses of the rounds still in flight (pipelined mode) and surface device-side errors."""
+        out = self._collect_losses(self._e2e_rounds)
+        self.check_health()
+        return out
 
     def close(self):
         if getattr(self.agg, "inplace", False):          # parameters live in the arena: move them out before it is freed

@@ -32,6 +32,15 @@ _CUDA_SIGS = {
     "cs_tiny_ecg_backward": (i32, [vp, vp, i32, i32, i32, i32, vp, vp, vp, i32, vp]),
     "cs_tiny_ecg_train_step": (i32, [vp, vp, vp, i32, i32, i32, i32, vp, vp, vp, vp, vp, f32, f32, f32,
                                      i32, i32, f32, f32, i32, vp]),
+    "cs_tiny_ecg_round_scratch_floats": (sz, [i32]),
+    "cs_perm_index": (C.c_uint64, [C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64]),
+    "cs_tiny_ecg_train_round": (i32, [vp, vp, vp, i32, i64, i32, i32, i32, i32, i32, C.c_uint64, vp, vp, vp, vp, vp,
+                                      f32, f32, f32, i32, i32, f32, f32, i32, vp, vp, f32, i32, f32, i32, sz, i32, vp]),
+    "cs_tiny_ecg_train_round_local": (i32, [C.POINTER(vp), i32, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), i32,
+                                            C.POINTER(i64), i32, i32, i32, i32, i32, C.POINTER(C.c_uint64),
+                                            C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp),
+                                            f32, f32, f32, i32, i32, f32, f32, i32, C.POINTER(vp), C.POINTER(f32),
+                                            i32, f32, i32, sz, i32, vp]),
     "cs_cross_entropy_fwd_bwd": (i32, [vp, vp, i32, i32, vp, vp, vp, vp]),
     "cs_sgd_momentum": (i32, [vp, vp, vp, i64, f32, f32, f32, i32, vp, vp, f32, f32, i32, vp, vp]),
     "cs_conv1d_fwd": (i32, [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, vp]),
@@ -66,6 +75,8 @@ _CUDA_SIGS = {
     "cs_comm_arena_bytes": (sz, [vp]),
     "cs_comm_destroy": (i32, [vp]),
     "cs_comm_status": (i32, [vp, C.POINTER(i32)]),
+    "cs_comm_set_timeout_ms": (i32, [vp, C.c_longlong]),
+    "cs_comm_clear_status": (i32, [vp]),
     "cs_comm_barrier": (i32, [vp, i32, vp]),
     "cs_fedavg_arena_bytes": (sz, [i64, i32, i32]),
     "cs_fedavg_aggregate": (i32, [vp, vp, vp, i64, f32, i32, f32, vp, sz, i32, vp]),

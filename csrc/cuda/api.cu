@@ -62,6 +62,8 @@ int comm_create_local(int, size_t, cs_comm**);
 int comm_destroy(cs_comm*);
 int comm_barrier(cs_comm*, int, cudaStream_t);
 int comm_status(cs_comm*, int*);
+int comm_set_timeout_ms(cs_comm*, long long);
+int comm_clear_status(cs_comm*);
 size_t agg_arena_need(long long, int, int);
 int fedavg_aggregate(cs_comm*, float*, float*, long long, float, int, float, float*, size_t, int, float, cudaStream_t);
 int fedavg_aggregate_local(cs_comm**, int, float* const*, float* const*, long long, const float*, int, float,
@@ -261,6 +263,8 @@ size_t cs_comm_arena_bytes(cs_comm_t* c) { return comm_bytes((cs_comm*)c); }
 int cs_comm_destroy(cs_comm_t* c) { return comm_destroy((cs_comm*)c); }
 int cs_comm_barrier(cs_comm_t* c, int channel, cs_stream_t s) { return comm_barrier((cs_comm*)c, channel, ST(s)); }
 int cs_comm_status(cs_comm_t* c, int* out) { return comm_status((cs_comm*)c, out); }
+int cs_comm_set_timeout_ms(cs_comm_t* c, long long ms) { return comm_set_timeout_ms((cs_comm*)c, ms); }
+int cs_comm_clear_status(cs_comm_t* c) { return comm_clear_status((cs_comm*)c); }
 size_t cs_fedavg_arena_bytes(int64_t n, int wire_bf16, int world) { return agg_arena_need(n, wire_bf16, world); }
 
 int cs_fedavg_aggregate(cs_comm_t* c, float* local, float* prev, int64_t n, float weight, int wire_bf16,

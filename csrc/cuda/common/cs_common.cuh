@@ -39,7 +39,7 @@ struct TinyLayout {
 };
 
 // ctrl / fstate slots of the on-device training state (see include/crossscale.h)
-enum { CTRL_TICKET = 0, CTRL_GROWTH = 1, CTRL_STEPS = 2, CTRL_SKIPPED = 3, CTRL_FOUND_INF = 4 };
+enum { CTRL_TICKET = 0, CTRL_GROWTH = 1, CTRL_STEPS = 2, CTRL_SKIPPED = 3, CTRL_FOUND_INF = 4, CTRL_ERROR = 5, CTRL_POS = 6 /* int64: samples drawn so far (in-kernel permutation sampler) */ };
 enum { FS_LOSS_SUM = 0, FS_SCALE = 1, FS_LAST_LOSS = 2, FS_LOSS_STEP = 3 };
 
 __device__ __forceinline__ float warp_sum(float v) {

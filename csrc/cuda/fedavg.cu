@@ -15,72 +15,23 @@
 // Two-shot (large n, bandwidth bound): reduce-scatter by P2P loads of slice `rank` from every
 // peer, all-gather by P2P stores of the reduced slice into every peer — (P-1)/P * n elements in and
 // out per GPU, the bandwidth-optimal volume without in-switch reduction.
-#include "common/cs_common.cuh"
+#include "comm_dev.cuh"
 
+#include <stdlib.h>
 #include <string.h>
 #include <vector>
 
 namespace cs {
 
-constexpr int kMaxRanks = CS_MAX_RANKS;
-constexpr int kChannels = 8;          // independent barrier channels (streams / buckets in flight)
-constexpr int kMaxBlocks = 160;       // blocks per collective kernel (a block only ever waits for the same block on peers)
-constexpr int kCommThreads = 512;
-constexpr size_t kSignalWords = (size_t)kChannels * kMaxBlocks * kMaxRanks;
-constexpr int64_t kOneShotMaxElems = 64 * 1024;   // 256 KiB of fp32
-
-struct CommDev {                      // lives in device memory, one per rank
-    int rank, world;
-    char* arena[kMaxRanks];           // peer-mapped arenas (arena[rank] is local)
-    uint32_t* signals[kMaxRanks];     // peer-mapped signal pads
-    uint32_t* epochs;                 // local: [kChannels][kMaxBlocks] barrier epochs
-    int* status;                      // local: != 0 after a barrier timeout
-    size_t arena_bytes;
-};
-
-}  // namespace cs
-
-struct cs_comm {
-    int rank = 0, world = 1;
-    size_t bytes = 0;
-    int device = 0;
-    bool emulated = false;            // all ranks on one device (tests / single GPU)
-    void* arena = nullptr;
-    uint32_t* signals = nullptr;
-    uint32_t* epochs = nullptr;
-    int* status = nullptr;
-    void* peer_arena[cs::kMaxRanks] = {};
-    uint32_t* peer_signals[cs::kMaxRanks] = {};
-    bool opened[cs::kMaxRanks] = {};
-    cs::CommDev* dev = nullptr;       // device copy of the context
-    cs_comm** group = nullptr;        // emulation: all members (owned by member 0)
-    cs::CommDev* group_dev = nullptr; // emulation: contiguous array of `world` contexts
-};
-
-namespace cs {
-
-// ------------------------------------------------------------------------------------------------
-// device-side primitives
-// ------------------------------------------------------------------------------------------------
-__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
-    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
-    uint32_t v;
-    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ unsigned long long globaltimer_ns() {
-    unsigned long long t;
-    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
-    return t;
-}
-
 // Cross-GPU barrier between block `b` of every rank on channel `ch`.  Epochs are kept in device
 // memory (not kernel arguments) so that a captured CUDA graph can be replayed.
-__device__ __forceinline__ void xgpu_barrier(const CommDev& c, int ch, int b, uint32_t epoch) {
+// Returns false (to every thread of the block) when a peer's flag did not arrive within the communicator's time-out:
+// the status word is raised and the caller must NOT consume peer data - it skips its reduction / write-back so that
+// the local model stays what local training left, instead of a sum over stale slots.
+__device__ __forceinline__ bool xgpu_barrier(const CommDev& c, int ch, int b, uint32_t epoch) {
     __syncthreads();
     const int t = threadIdx.x;
+    int late = 0;
     if (t < c.world) {
         const size_t base = ((size_t)ch * kMaxBlocks + b) * kMaxRanks;
         __threadfence_system();
@@ -88,10 +39,10 @@ __device__ __forceinline__ void xgpu_barrier(const CommDev& c, int ch, int b, ui
         const uint32_t* mine = c.signals[c.rank] + base + t;
         const unsigned long long t0 = globaltimer_ns();
         while ((int32_t)(ld_acquire_sys(mine) - epoch) < 0) {
-            if (globaltimer_ns() - t0 > 4000000000ull) { atomicExch(c.status, 1); break; }  // 4 s: never hang the box
+            if (globaltimer_ns() - t0 > c.timeout_ns) { *(volatile int*)c.status = 1; late = 1; break; }   // never hang the box
         }
     }
-    __syncthreads();
+    return __syncthreads_or(late) == 0;
 }
 
 struct AggCall {                       // per-call arguments; arrays indexed by emulated rank (blockIdx.y)
@@ -105,18 +56,6 @@ struct AggCall {                       // per-call arguments; arrays indexed by 
     int wire_bf16;
     int channel;
     size_t arena_off;
-};
-
-template <bool BF16> struct Wire;
-template <> struct Wire<false> {
-    using T = float;
-    __device__ static T enc(float v) { return v; }
-    __device__ static float dec(T v) { return v; }
-};
-template <> struct Wire<true> {
-    using T = __nv_bfloat16;
-    __device__ static T enc(float v) { return __float2bfloat16(v); }
-    __device__ static float dec(T v) { return __bfloat162float(v); }
 };
 
 // ------------------------------------------------------------------------------------------------
@@ -149,7 +88,7 @@ __global__ void __launch_bounds__(kCommThreads) fedavg_oneshot_kernel(const Comm
             dst[i] = e;
         }
     }
-    xgpu_barrier(c, a.channel, b, epoch);
+    if (!xgpu_barrier(c, a.channel, b, epoch)) { if (threadIdx.x == 0) *ep = epoch; return; }   // peer missing: keep the local model
     // phase 2: reduce the P slots that landed in my arena, apply the server update in place
     const T* base = reinterpret_cast<const T*>(c.arena[c.rank] + a.arena_off) + (size_t)parity * P * slot_elems;
     for (long long i = lo + threadIdx.x; i < hi; i += blockDim.x) {
@@ -251,7 +190,7 @@ __global__ void __launch_bounds__(kCommThreads) fedavg_twoshot_kernel(const Comm
             }
         }
     }
-    xgpu_barrier(c, a.channel, b, e0 + 1);
+    if (!xgpu_barrier(c, a.channel, b, e0 + 1)) { if (threadIdx.x == 0) *ep = e0 + 2; return; }
     // phase 2: reduce my slice from every peer's IN (P2P loads), push the result into every peer's OUT
     {
         const int s = c.rank;
@@ -281,7 +220,7 @@ __global__ void __launch_bounds__(kCommThreads) fedavg_twoshot_kernel(const Comm
             }
         }
     }
-    xgpu_barrier(c, a.channel, b, e0 + 2);
+    if (!xgpu_barrier(c, a.channel, b, e0 + 2)) { if (threadIdx.x == 0) *ep = e0 + 2; return; }
     // phase 3: local server update from OUT
     for (int s = 0; s < P; ++s) {
         const long long g0 = s * gps + (long long)b * gpb;
@@ -340,7 +279,7 @@ __global__ void __launch_bounds__(kCommThreads) fedavg_inplace_kernel(const Comm
     const long long gps = (n4 + P - 1) / P, gpb = (gps + nb - 1) / nb;
     float* prev = a.prev[er];
     float* mom = a.mom[er];
-    xgpu_barrier(c, a.channel, b, e0 + 1);                   // every rank's local training is complete
+    if (!xgpu_barrier(c, a.channel, b, e0 + 1)) { if (threadIdx.x == 0) *ep = e0 + 2; return; }   // every rank's local training is complete
     {
         const int s = c.rank;
         const long long g0 = s * gps + (long long)b * gpb;
@@ -435,7 +374,22 @@ __global__ void __launch_bounds__(kCommThreads) fedavg_nvls_kernel(const CommDev
             }
         }
     }
-    xgpu_barrier(c, a.channel, b, e0 + 1);
+    if (!xgpu_barrier(c, a.channel, b, e0 + 1)) {               // peer missing: undo the pre-scaling, touch nothing else
+        if (a.prescale != 1.0f) {
+            const float inv = 1.0f / a.prescale;
+            for (int s = 0; s < P; ++s) {
+                const long long g0 = s * gps + (long long)b * gpb;
+                long long g1 = g0 + gpb; if (g1 > (s + 1) * gps) g1 = (s + 1) * gps; if (g1 > n4) g1 = n4;
+                for (long long g = g0 + tid; g < g1; g += T) {
+                    float4 v = reinterpret_cast<float4*>(a.local)[g];
+                    v.x *= inv; v.y *= inv; v.z *= inv; v.w *= inv;
+                    reinterpret_cast<float4*>(a.local)[g] = v;
+                }
+            }
+        }
+        if (threadIdx.x == 0) *ep = e0 + 2;
+        return;
+    }
     {
         const int s = c.rank;
         const long long g0 = s * gps + (long long)b * gpb;
@@ -489,8 +443,10 @@ static int alloc_rank(cs_comm* c) {
     CS_CUDA_OK(cudaMemset(c->signals, 0, kSignalWords * sizeof(uint32_t)));
     CS_CUDA_OK(cudaMalloc((void**)&c->epochs, kChannels * kMaxBlocks * sizeof(uint32_t)));
     CS_CUDA_OK(cudaMemset(c->epochs, 0, kChannels * kMaxBlocks * sizeof(uint32_t)));
-    CS_CUDA_OK(cudaMalloc((void**)&c->status, sizeof(int)));
-    CS_CUDA_OK(cudaMemset(c->status, 0, sizeof(int)));
+    CS_CUDA_OK(cudaHostAlloc((void**)&c->status_host, sizeof(int), cudaHostAllocMapped));
+    *c->status_host = 0;
+    CS_CUDA_OK(cudaHostGetDevicePointer((void**)&c->status, c->status_host, 0));
+    if (const char* e = getenv("CS_COMM_TIMEOUT_MS")) { const long long ms = atoll(e); if (ms > 0) c->timeout_ns = (unsigned long long)ms * 1000000ull; }
     CS_CUDA_OK(cudaMalloc((void**)&c->dev, sizeof(CommDev)));
     return CS_OK;
 }
@@ -498,7 +454,7 @@ static int alloc_rank(cs_comm* c) {
 static int upload_ctx(cs_comm* c, CommDev* dst) {
     CommDev h;
     memset(&h, 0, sizeof(h));
-    h.rank = c->rank; h.world = c->world; h.epochs = c->epochs; h.status = c->status; h.arena_bytes = c->bytes;
+    h.rank = c->rank; h.world = c->world; h.epochs = c->epochs; h.status = c->status; h.arena_bytes = c->bytes; h.timeout_ns = c->timeout_ns;
     for (int r = 0; r < c->world; ++r) { h.arena[r] = (char*)c->peer_arena[r]; h.signals[r] = c->peer_signals[r]; }
     CS_CUDA_OK(cudaMemcpy(dst, &h, sizeof(h), cudaMemcpyHostToDevice));
     return CS_OK;
@@ -572,7 +528,7 @@ int comm_destroy(cs_comm* c) {
         cs_comm** g = c->group; int world = c->world;
         cudaFree(c->group_dev);
         for (int r = 0; r < world; ++r) {
-            cudaFree(g[r]->arena); cudaFree(g[r]->signals); cudaFree(g[r]->epochs); cudaFree(g[r]->status); cudaFree(g[r]->dev);
+            cudaFree(g[r]->arena); cudaFree(g[r]->signals); cudaFree(g[r]->epochs); cudaFreeHost(g[r]->status_host); cudaFree(g[r]->dev);
             delete g[r];
         }
         delete[] g;
@@ -580,7 +536,7 @@ int comm_destroy(cs_comm* c) {
     }
     for (int r = 0; r < c->world; ++r)
         if (c->opened[r]) { cudaIpcCloseMemHandle(c->peer_arena[r]); cudaIpcCloseMemHandle(c->peer_signals[r]); }
-    cudaFree(c->arena); cudaFree(c->signals); cudaFree(c->epochs); cudaFree(c->status); cudaFree(c->dev);
+    cudaFree(c->arena); cudaFree(c->signals); cudaFree(c->epochs); cudaFreeHost(c->status_host); cudaFree(c->dev);
     delete c;
     return CS_OK;
 }
@@ -718,8 +674,28 @@ int comm_barrier(cs_comm* c, int channel, cudaStream_t st) {
     return CS_OK;
 }
 
+// The status word lives in host-mapped pinned memory: reading it costs nothing and synchronises nothing.  It is
+// meaningful for kernels the caller has already synchronised with (every round of FedAvgRunner.run_round does).
 int comm_status(cs_comm* c, int* out) {
-    CS_CUDA_OK(cudaMemcpy(out, c->status, sizeof(int), cudaMemcpyDeviceToHost));
+    CS_REQUIRE(c && out, "comm_status: null");
+    *out = *(volatile int*)c->status_host;
+    return CS_OK;
+}
+int comm_set_timeout_ms(cs_comm* c, long long ms) {
+    CS_REQUIRE(c && ms > 0, "comm_set_timeout: bad arguments");
+    cs_comm** members = c->emulated ? c->group : &c;
+    const int n = c->emulated ? c->world : 1;
+    for (int r = 0; r < n; ++r) {
+        members[r]->timeout_ns = (unsigned long long)ms * 1000000ull;
+        const unsigned long long v = members[r]->timeout_ns;
+        CS_CUDA_OK(cudaMemcpy(&members[r]->dev->timeout_ns, &v, sizeof(v), cudaMemcpyHostToDevice));
+        if (c->emulated) CS_CUDA_OK(cudaMemcpy(&c->group_dev[r].timeout_ns, &v, sizeof(v), cudaMemcpyHostToDevice));
+    }
+    return CS_OK;
+}
+int comm_clear_status(cs_comm* c) {
+    CS_REQUIRE(c != nullptr, "comm_clear_status: null");
+    *(volatile int*)c->status_host = 0;
     return CS_OK;
 }
 

@@ -81,7 +81,11 @@ __global__ void __launch_bounds__(kThreads, 2) tiny_ecg_f32_kernel(TinyArgs a) {
             for (int l = tid; l < L; l += kThreads) xs[l + 3] = __ldg(xr + l);
         }
         int label = 0;
-        if (MODE == MODE_TRAIN) label = (int)a.y[row];
+        if (MODE == MODE_TRAIN) {
+            label = (int)a.y[row];
+            // a label outside [0, C) would index the logits out of bounds: train it as class 0 and raise the error bit
+            if ((unsigned)label >= (unsigned)C) { if (threadIdx.x == 0) atomicOr(a.ctrl + CTRL_ERROR, 1); label = 0; }
+        }
         __syncthreads();
 
         // ---- conv1 (1->16, k7, pad 3) + ReLU --------------------------------------------------

@@ -43,7 +43,8 @@ struct Mapped {
         if (base == MAP_FAILED) { base = nullptr; err = "mmap failed " + path; close(); return false; }
         madvise(base, size, MADV_SEQUENTIAL);
         memcpy(&n, base, 8); memcpy(&l, (char*)base + 8, 8);
-        if (n < 0 || l <= 0 || (size_t)(16 + n * l * 4) > size) { err = "shard header/payload mismatch " + path; close(); return false; }
+        // overflow-safe: compare n against the number of windows the payload can hold (a corrupt header must not wrap)
+        if (n < 0 || l <= 0 || (uint64_t)l > (size - 16) / 4 || (uint64_t)n > (size - 16) / 4 / (uint64_t)l) { err = "shard header/payload mismatch " + path; close(); return false; }
         // optional label sidecar: <stem>.lbl = [int64 N][int64 classes][N uint8]
         std::string lp = path;
         size_t dot = lp.rfind('.');
@@ -205,7 +206,11 @@ int cs_prefetcher_recycle(cs_prefetcher_t* p, int slot) {
 
 void cs_prefetcher_destroy(cs_prefetcher_t* p) {
     if (!p) return;
-    p->stop.store(true);
+    {   // set the flag under the mutex the worker's predicates are checked under: a store + notify that lands between the
+        // worker's predicate check and its wait would otherwise be lost and join() below would hang forever
+        std::lock_guard<std::mutex> g(p->mu);
+        p->stop.store(true);
+    }
     p->cv_free.notify_all(); p->cv_full.notify_all();
     if (p->th.joinable()) p->th.join();
     delete p;

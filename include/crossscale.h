@@ -60,7 +60,7 @@ int cs_gather_rows(const float* x, const int64_t* y, const int64_t* idx, void* x
 size_t cs_tiny_ecg_smem_bytes(int L, int C, int amp);
 
 /* floats the `gacc` gradient scratch of cs_tiny_ecg_train_step must hold (zeroed once by the caller;
- * every step leaves it zero).  The tcgen05 kernel keeps 8 TMEM-shaped replicas there. */
+ * every step leaves it zero).  The tcgen05 kernel keeps 4 TMEM-shaped replicas of 1792 floats there. */
 size_t cs_tiny_ecg_scratch_floats(int C);
 
 /* logits[B,C] = TinyECG(x) */
@@ -77,7 +77,8 @@ int cs_tiny_ecg_backward(const void* x, const int64_t* idx, int x_bf16, int B, i
  *   y      labels, indexed like x (y[idx[b]] or y[b])
  *   mom    momentum buffer  [P]        gacc   gradient scratch, cs_tiny_ecg_scratch_floats(C) floats,
  *                                              zero on first use; the kernel leaves it zero again
- *   ctrl   int32[8]  {ticket, growth_tracker, steps_done, skipped_steps, found_inf, ...}
+ *   ctrl   int32[8]  {ticket, growth_tracker, steps_done, skipped_steps, found_inf, error_bits,
+ *                      samples_drawn (int64 in slots 6-7)}      error_bits: CS_TINY_ERR_*
  *   fstate fp32[8]   {loss_sum, loss_scale, last_loss, loss_step_scratch, ...}
  * SGD: buf = momentum*buf + (g + wd*p); p -= lr*buf            (torch.optim.SGD, ref :181)
  * scaler (use_scaler != 0): torch.cuda.amp.GradScaler semantics  (ref :121-127)            */
@@ -102,6 +103,52 @@ int cs_tiny_ecg_train_step_noalloc(const void* x, const int64_t* y, const int64_
                                    float* fstate, float lr, float momentum, float wd, int amp,
                                    int use_scaler, float growth, float backoff, int growth_interval,
                                    cs_stream_t stream);
+
+/* device-side error bits the fused TinyECG kernels OR into ctrl[5] (0 = healthy).  The Python wrappers
+ * read the word whenever they read the round's loss and raise. */
+#define CS_TINY_ERR_LABEL 1 /* a label outside [0, C): the sample was trained as class 0                  */
+#define CS_TINY_ERR_MBAR  2 /* an mbarrier wait inside the CTA timed out (protocol bug / hardware fault)   */
+#define CS_TINY_ERR_GRID  4 /* the grid-wide step barrier timed out                                        */
+#define CS_TINY_ERR_PEER  8 /* fused aggregation: a peer's flag never arrived; the local model was kept    */
+
+/* K6b persistent: ONE cooperative launch = `steps` local training steps + (optionally) the FedAvg aggregation.
+ * ref: the whole round loop body, TRUE_FL_M3/part3_fedavg_overlap_mpi_gpu.py:186-231 (Bcast, 50 x train_step_G1,
+ * Allreduce-mean) - here 50 steps x ~40 launches, 50 synchronisations and 36 host-staged collectives become one kernel.
+ * tcgen05 path only (amp = CS_AMP_BF16 / CS_AMP_FP16; CS_ERR_INVALID otherwise).  Per step: fused forward/backward
+ * per sample, gradients summed through a rotating global scratch, one grid-wide barrier, then every CTA applies
+ * SGD-momentum (and the GradScaler rules) to its own shared-memory copy of the model.
+ *   sample_mode 0: sample b of step s reads row idx[s*B + b]            (idx int64 [steps*B])
+ *               1: row s*B + b of x (a staged block of steps*B rows; n_rows = rows in the block or 0)
+ *               2: in-kernel per-epoch permutation of the n_rows dataset rows (ragged tail dropped, like
+ *                  make_gpu_batch_iter, Module_3/shard_dataset.py:118-136): row = cs_perm_index(pos % usable, n_rows,
+ *                  seed, pos / usable), usable = n_rows / B * B, pos = ctrl[6..7] (int64), advanced by steps*B per call
+ *   gacc   cs_tiny_ecg_round_scratch_floats(C) floats, zero before the first call; left zero
+ *   ctrl / fstate / SGD / scaler: as cs_tiny_ecg_train_step (fstate[0] += sum of the steps' mean losses)
+ *   comm != NULL: the round ends in the one-shot aggregation of cs_fedavg_aggregate (same arena layout, flags and
+ *   epoch word: the two are interchangeable on a channel): theta <- prev + server_lr * sum_i weight_i (theta_i - prev),
+ *   written to params and prev; momentum is zeroed when reset_momentum != 0.  comm == NULL: params/mom are written back.
+ * Every CTA of the launch must be co-resident (cooperative launch; grid = min(B, 2 x SMs)). */
+size_t cs_tiny_ecg_round_scratch_floats(int C);
+struct cs_comm;
+int cs_tiny_ecg_train_round(const void* x, const int64_t* y, const int64_t* idx, int x_bf16, int64_t n_rows,
+                            int B, int L, int C, int steps, int sample_mode, uint64_t seed, float* params,
+                            float* mom, float* gacc, int32_t* ctrl, float* fstate, float lr, float momentum,
+                            float wd, int amp, int use_scaler, float growth, float backoff, int growth_interval,
+                            struct cs_comm* comm, float* prev, float weight, int wire_bf16, float server_lr,
+                            int reset_momentum, size_t arena_off, int channel, cs_stream_t stream);
+/* the same for `world` emulated clients on ONE device (arrays indexed by client; blockIdx.y = client; all CTAs of all
+ * clients co-resident, so B * world <= 2 x SMs): the cross-client flag protocol runs inside one cooperative launch */
+int cs_tiny_ecg_train_round_local(struct cs_comm** group, int world, const void* const* x, const int64_t* const* y,
+                                  const int64_t* const* idx, int x_bf16, const int64_t* n_rows, int B, int L, int C,
+                                  int steps, int sample_mode, const uint64_t* seeds, float* const* params,
+                                  float* const* mom, float* const* gacc, int32_t* const* ctrl, float* const* fstate,
+                                  float lr, float momentum, float wd, int amp, int use_scaler, float growth,
+                                  float backoff, int growth_interval, float* const* prev, const float* weights,
+                                  int wire_bf16, float server_lr, int reset_momentum, size_t arena_off, int channel,
+                                  cs_stream_t stream);
+/* the sampler's bijection on [0, n) (host-callable mirror of the device function) */
+unsigned long long cs_perm_index(unsigned long long i, unsigned long long n, unsigned long long seed,
+                                 unsigned long long epoch);
 
 /* ---------------------------------------------------------------------------------------------
  * K5   head-less cross entropy + loss scale, and AMP unscale / inf-check / scale update
@@ -253,6 +300,10 @@ int cs_comm_destroy(cs_comm_t* c);
 
 /* != 0 after a device-side barrier timed out (a peer never arrived); sticky */
 int cs_comm_status(cs_comm_t* c, int* status_out);
+/* how long a cross-GPU flag wait may spin before it gives up, raises the status word and SKIPS its reduction / write-back
+ * (default 4000 ms, or the environment variable CS_COMM_TIMEOUT_MS at creation) */
+int cs_comm_set_timeout_ms(cs_comm_t* c, long long ms);
+int cs_comm_clear_status(cs_comm_t* c);
 
 /* K9: device-side barrier across ranks (one tiny kernel; st.release.sys / ld.acquire.sys flags in
  * the peers' signal pads).  `channel` (0..7) selects an independent flag set so collectives on

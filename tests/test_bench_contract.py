@@ -48,7 +48,7 @@ def test_header_declares_every_exported_cuda_symbol():
     hdr = open(os.path.join(REPO, "include", "crossscale.h")).read()
     declared = set(re.findall(r"\b(cs_[a-z0-9_]+)\s*\(", hdr))
     defined = set()
-    for f in ("api.cu", "tiny_ecg_noalloc.cu"):
+    for f in ("api.cu", "tiny_ecg_noalloc.cu", "tiny_ecg_round.cu"):
         src = open(os.path.join(REPO, "csrc", "cuda", f)).read()
         defined |= set(re.findall(r"^(?:extern \"C\" )?(?:int|size_t|void\*?|const char\*)\s+(cs_[a-z0-9_]+)\s*\(", src, flags=re.M))
     missing = sorted(d for d in defined - declared if not d.startswith("cs_debug"))

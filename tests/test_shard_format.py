@@ -101,3 +101,25 @@ def test_shard_prep_module_imports_cleanly():
     import importlib
     importlib.import_module("crossscale.data.shard_prep")
     importlib.import_module("crossscale.cli.shard_prep")
+
+
+def test_stale_label_sidecar_is_never_paired_with_new_windows(tmp_path):
+    """re-preparing an unlabelled data set into a directory that held a labelled one must not keep the
+    old .lbl files, and a sidecar whose count disagrees with the shard is ignored."""
+    import numpy as np
+    from crossscale.data import shard_format as fmt
+    from crossscale.data.shard_dataset import ShardDataset
+    p = str(tmp_path / fmt.shard_name(0))
+    fmt.write_shard(p, np.zeros((100, 64), np.float32), labels=np.arange(100) % 5, num_classes=5)
+    assert fmt.load_labels(p) is not None
+    fmt.write_shard(p, np.ones((300, 64), np.float32))               # same name, no labels
+    assert not os.path.exists(fmt.label_path_for(p))
+    ds = ShardDataset([p])
+    assert ds.x.shape == (300, 64) and ds.y.shape == (300,) and not ds.has_labels
+    # a sidecar of the wrong length (left by another tool) is ignored with a warning
+    fmt.write_shard(p, np.zeros((100, 64), np.float32), labels=np.arange(100) % 5, num_classes=5)
+    lbl = open(fmt.label_path_for(p), "rb").read()
+    fmt.write_shard(p, np.ones((300, 64), np.float32))
+    open(fmt.label_path_for(p), "wb").write(lbl)
+    with pytest.warns(UserWarning):
+        assert fmt.load_labels(p) is None
