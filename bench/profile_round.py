@@ -88,21 +88,39 @@ torch.cuda.synchronize()
 graph_ms = e0.elapsed_time(e1) / a.rounds
 clocks = sampler.stop()
 
-prof = torch.zeros(1024, dtype=torch.int64, device=dev)
+# fixed cost vs per-step cost: rounds of 1, 2, 5, 10, 25 steps
+step_scan = {}
+for ns in (1, 2, 5, 10, 25, a.steps):
+    idx_s = idx[: ns * a.batch]
+    for _ in range(5):
+        st.round(data, lab, ns, a.batch, idx=idx_s if a.mode == tk.SAMPLE_IDX else None, sample_mode=a.mode, seed=77)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(20):
+        st.round(data, lab, ns, a.batch, idx=idx_s if a.mode == tk.SAMPLE_IDX else None, sample_mode=a.mode, seed=77)
+    e1.record()
+    torch.cuda.synchronize()
+    step_scan[ns] = round(e0.elapsed_time(e1) / 20 * 1e3, 2)
+
+prof = torch.zeros(4096, dtype=torch.int64, device=dev)
 lib.cs_debug_set_tiny_profile.argtypes = [ctypes.c_void_p]
 lib.cs_debug_set_tiny_profile(prof.data_ptr())
 one_round()
 torch.cuda.synchronize()
 lib.cs_debug_set_tiny_profile(None)
 pt = prof.cpu().tolist()
-names = {0: "step start (planes free)", 1: "xs + im2col plane staged", 2: "grid barrier + replica sum + SGD + W2 repack",
+names = {0: "step start", 1: "xs + im2col plane staged", 2: "grid barrier wait + replica sum + SGD + W2 repack",
          3: "conv1 -> h1 planes, handoff", 4: "conv2 fwd MMAs done", 5: "epilogue 1 + pool", 6: "head + CE",
          7: "head grads + dz2 planes, handoff", 8: "dgrad MMAs done", 9: "epilogue 2 dz1 planes, handoff",
          10: "all wgrad MMAs done", 11: "readout + reductions + arrive"}
 order = [0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11]
 phases = [(names[k], pt[k] - pt[order[i - 1]]) for i, k in enumerate(order) if i > 0 and pt[k] and pt[order[i - 1]]]
-arr = np.array(pt[64:64 + min(a.batch, 296)])
-arr = arr[arr > 0]
+lib.cs_debug_last_round_grid.restype = ctypes.c_int
+nc = int(lib.cs_debug_last_round_grid())
+per = np.array(pt[1024:1024 + 4 * nc]).reshape(nc, 4)
+t0 = per[:, 0].min()
+start, arrive, passed = per[:, 0] - t0, per[:, 1] - t0, per[:, 2] - t0
+arr = per[:, 1]
 out = {"amp": a.amp, "B": a.batch, "L": a.L, "steps": a.steps, "sample_mode": a.mode,
        "round_ms_median": float(np.median(times)), "round_ms_min": min(times), "round_ms_max": max(times),
        "us_per_step": float(np.median(times)) / a.steps * 1e3,
@@ -113,5 +131,9 @@ out = {"amp": a.amp, "B": a.batch, "L": a.L, "steps": a.steps, "sample_mode": a.
        "barrier_wait_to_update_cycles": (pt[21] - pt[20]) if pt[21] and pt[20] else None,
        "arrive_spread_ns": int(arr.max() - arr.min()) if arr.size else None,
        "arrive_p50_after_first_ns": int(np.median(arr) - arr.min()) if arr.size else None,
+       "grid_ctas": nc, "us_per_round_by_steps": step_scan,
+       "cta_step_start_ns": {"min": int(start.min()), "p50": int(np.median(start)), "max": int(start.max())},
+       "cta_work_ns(start->arrive)": {"min": int((arrive - start).min()), "p50": int(np.median(arrive - start)), "max": int((arrive - start).max())},
+       "cta_barrier_passed_ns(after step start)": {"min": int(passed.min()), "p50": int(np.median(passed)), "max": int(passed.max())},
        "loss_sum": st.loss_sum()}
 print(json.dumps(out, indent=1))
