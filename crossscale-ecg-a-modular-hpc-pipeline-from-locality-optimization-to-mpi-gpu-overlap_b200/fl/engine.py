@@ -160,12 +160,45 @@ class KernelLocalTrainer:
             elif isinstance(mod, BNReLU1d):
                 mod.fused_grad = True                       # dgamma / dbeta are added into the arena by the reduction kernel
         self.sync = None
+        self.bucket_bytes, self.sync_grads = bucket_bytes, bool(sync_grads)
         if sync_grads:
             from ..parallel.grad_sync import GradSync
             self.sync = GradSync(self.flat, bucket_bytes=bucket_bytes, wire=wire)
         self.launches = 0
         # whole-step CUDA graph (forward + backward + bucket all-reduces + SGD): ~600 launches become one replay
         self.use_graph, self._graph, self._warm = bool(use_graph), None, 0
+        self._fused = None            # set by enable_fused_aggregation: the round's last step ends in the bucketed FedAvg
+        self._graph_f, self._warm_f = None, 0
+
+    fused_max_blocks = 48             # CTAs per bucket launch: enough to fill NVLink, few enough to leave backward its SMs
+
+    def enable_fused_aggregation(self, agg, prev: Optional[torch.Tensor]) -> bool:
+        """Let the LAST local step of a round carry the aggregation: each gradient bucket, as soon as backward has
+        produced it, gets ONE launch on a side stream that applies the optimizer step to the bucket, averages it
+        across clients in place over NVLink and refreshes its bf16 shadow (``cs_fedavg_bucket``).  Needs the
+        parameters in the aggregator's symmetric arena (in-place P2P mode), no loss scaler, no momentum reset and no
+        per-step gradient all-reduce.  Returns whether the fused path is active."""
+        if (self.use_scaler or self.sync_grads or not getattr(agg, "inplace", False) or agg.nvls is not None
+                or agg.reset_momentum):
+            return False
+        if self.flat.flat.data_ptr() != agg.param_view.data_ptr():
+            return False
+        from ..parallel.grad_sync import GradSync
+        if self.sync is None:
+            self.sync = GradSync(self.flat, bucket_bytes=self.bucket_bytes, backend="off")
+        self._fused = {"agg": agg, "prev": prev}
+        return True
+
+    def _fused_bucket_op(self, j, b, ch, side) -> None:
+        f = self._fused
+        agg = f["agg"]
+        lo, n = b["lo_al"], b["hi_al"] - b["lo_al"]
+        use_prev = agg.server_lr != 1.0 and f["prev"] is not None
+        self._lib.check(self._lib.cuda_lib().cs_fedavg_bucket(
+            agg.comm.handle, lo * 4, self.flat.grad.data_ptr() + lo * 4, self.mom.data_ptr() + lo * 4,
+            (f["prev"].data_ptr() + lo * 4) if use_prev else None, self.shadow.data_ptr() + lo * 2, n, agg._weights,
+            self.lr, self.momentum, 0.0, 1.0, agg.server_lr, 1, ch, self.fused_max_blocks, side.cuda_stream), "cs_fedavg_bucket")
+        agg.launches += 1
 
     def flat_parameters(self) -> torch.Tensor:
         return self.flat.flat
@@ -179,7 +212,9 @@ class KernelLocalTrainer:
         """after the parameters changed outside the optimizer (aggregation, checkpoint load, arena rebind)"""
         self.shadow.copy_(self.flat.flat)
 
-    def step(self, x, y) -> torch.Tensor:
+    def step(self, x, y, fused_agg: bool = False) -> torch.Tensor:
+        if fused_agg:
+            return self._step_fused_outer(x, y)
         if not self.use_graph:
             return self._step(x, y)
         if self._graph is None:
@@ -196,13 +231,38 @@ class KernelLocalTrainer:
         self._graph.replay()
         return self._sloss
 
-    def _step(self, x, y) -> torch.Tensor:
+    def _step_fused_outer(self, x, y) -> torch.Tensor:
+        """the round's last step: backward feeds the bucketed optimizer-step + aggregation launches (own CUDA graph)"""
+        assert self._fused is not None
+        if not self.use_graph:
+            return self._step(x, y, fused_agg=True)
+        if self._graph_f is None:
+            if self._warm_f < 2:
+                self._warm_f += 1
+                return self._step(x, y, fused_agg=True)
+            self._fx, self._fy = x.clone(), y.clone()
+            torch.cuda.synchronize()
+            self._graph_f = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self._graph_f):
+                self._floss = self._step(self._fx, self._fy, fused_agg=True)
+        self._fx.copy_(x)
+        self._fy.copy_(y)
+        self._graph_f.replay()
+        return self._floss
+
+    def _step(self, x, y, fused_agg: bool = False) -> torch.Tensor:
         self.model.train()
         self.flat.grad.zero_()
+        if self.sync is not None:
+            self.sync.fused_op = self._fused_bucket_op if fused_agg else None
         loss = _ScaledCE.apply(self.model(x), y, self.fstate[tk.FS_SCALE:tk.FS_SCALE + 1] if self.use_scaler else None)
         loss.backward()
         if self.sync is not None:
             self.sync.finish()
+            self.sync.fused_op = None
+        if fused_agg:                                       # optimizer step, aggregation and shadow refresh already happened per bucket
+            self.loss_sum += loss.detach()
+            return loss.detach()
         n = self.flat.flat.numel()
         self._lib.check(self._lib.cuda_lib().cs_sgd_momentum(
             self.flat.flat.data_ptr(), self.mom.data_ptr(), self.flat.grad.data_ptr(), n, self.lr, self.momentum, 0.0,
@@ -212,13 +272,13 @@ class KernelLocalTrainer:
         self.loss_sum += loss.detach()
         return loss.detach()
 
-    def run_steps(self, batch_iter: Iterator, steps: int) -> Tuple[float, int]:
+    def run_steps(self, batch_iter: Iterator, steps: int, fuse_last: bool = False) -> Tuple[float, int]:
         n = 0
         self.loss_sum.zero_()
-        for _ in range(steps):
+        for s in range(steps):
             x, y = next(batch_iter)
             n += x.size(0)
-            self.step(x, y)
+            self.step(x, y, fused_agg=(fuse_last and s == steps - 1 and self._fused is not None))
         return float(self.loss_sum.item()), n
 
 
@@ -365,7 +425,8 @@ class FedAvgRunner:
                  agg_backend: str = "auto", wire: str = "fp32", server_lr: float = 1.0,
                  reset_momentum: bool = False, use_graph: bool = True,
                  generator: Optional[torch.Generator] = None, model_name: str = "tiny_ecg",
-                 sync_grads: bool = False, inplace: str = "auto"):
+                 sync_grads: bool = False, inplace: str = "auto", fuse_bucket_agg: bool = True,
+                 bucket_bytes: int = 4 << 20):
         self.device = torch.device(device)
         self.model, self.rank, self.world = model, rank, world
         self.batch, self.local_steps, self.config = batch_size, local_steps, config
@@ -386,7 +447,7 @@ class FedAvgRunner:
             self.kernel_generic = (self.device.type == "cuda" and tk.use_kernels() and not isinstance(model, TinyECG))
             if self.kernel_generic:
                 self.trainer = KernelLocalTrainer(model, self.device, lr, momentum, use_scaler=(amp == "fp16"),
-                                                  sync_grads=sync_grads, use_graph=use_graph)
+                                                  sync_grads=sync_grads, use_graph=use_graph, bucket_bytes=bucket_bytes)
                 self.mom = self.trainer.mom
             else:
                 self.trainer = TorchLocalTrainer(model, self.device, lr, momentum,
@@ -409,6 +470,9 @@ class FedAvgRunner:
             self.agg.set_weights(self.weight)
         self.prev = self.flat.clone()
         self.rows: List[dict] = []
+        # large kernel-path models: the round's last step carries the bucketed aggregation (see KernelLocalTrainer)
+        self.fuse_bucket_agg = bool(not self.fused and getattr(self, "kernel_generic", False) and self.agg.inplace
+                                    and fuse_bucket_agg and self.trainer.enable_fused_aggregation(self.agg, self.prev))
         # TinyECG on the persistent round kernel: the aggregation rides in the tail of the same launch
         self.fuse_agg = (self.fused and self.trainer.use_round and self.agg.backend == "kernel" and not self.agg.inplace
                          and self.numel <= 4096)
@@ -443,14 +507,18 @@ class FedAvgRunner:
             # reference's CSV - local_train_ms, comm_ms - are measured; run_round_async fuses them)
             self.trainer.run_round_resident()
         else:
-            loss_acc, n_samples = self.trainer.run_steps(self.batch_iter, self.local_steps)
+            if self.fuse_bucket_agg:
+                loss_acc, n_samples = self.trainer.run_steps(self.batch_iter, self.local_steps, fuse_last=True)
+            else:
+                loss_acc, n_samples = self.trainer.run_steps(self.batch_iter, self.local_steps)
             self.flat = self.trainer.flat_parameters()   # (a view of the arena for the kernel trainer)
         t1 = time.perf_counter()
         if cuda:
             e1.record()
-        self.agg.aggregate(self.flat, self.prev, self.weight, self.mom)
-        if not self.fused:
-            self.trainer.load_flat(self.flat)
+        if not self.fuse_bucket_agg:                     # (fused: aggregated bucket by bucket under the last backward)
+            self.agg.aggregate(self.flat, self.prev, self.weight, self.mom)
+            if not self.fused:
+                self.trainer.load_flat(self.flat)
         if cuda:
             e2.record()
             torch.cuda.synchronize()

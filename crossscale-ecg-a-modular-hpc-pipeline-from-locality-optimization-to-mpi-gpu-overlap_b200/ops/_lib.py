@@ -77,6 +77,7 @@ _CUDA_SIGS = {
     "cs_comm_status": (i32, [vp, C.POINTER(i32)]),
     "cs_comm_set_timeout_ms": (i32, [vp, C.c_longlong]),
     "cs_comm_clear_status": (i32, [vp]),
+    "cs_debug_fedavg_aggregate_alone": (i32, [vp, vp, vp, i64, f32, vp, vp]),
     "cs_comm_barrier": (i32, [vp, i32, vp]),
     "cs_fedavg_arena_bytes": (sz, [i64, i32, i32]),
     "cs_fedavg_aggregate": (i32, [vp, vp, vp, i64, f32, i32, f32, vp, sz, i32, vp]),
@@ -86,6 +87,9 @@ _CUDA_SIGS = {
     "cs_fedavg_aggregate_inplace_local": (i32, [C.POINTER(vp), i32, sz, C.POINTER(vp), i64, C.POINTER(f32), f32,
                                                 C.POINTER(vp), i32, vp]),
     "cs_fedavg_aggregate_nvls": (i32, [vp, vp, vp, vp, i64, f32, f32, f32, vp, i32, vp]),
+    "cs_fedavg_bucket": (i32, [vp, sz, vp, vp, vp, vp, i64, C.POINTER(f32), f32, f32, f32, f32, f32, i32, i32, i32, vp]),
+    "cs_fedavg_bucket_local": (i32, [C.POINTER(vp), i32, sz, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), i64,
+                                     C.POINTER(f32), f32, f32, f32, f32, f32, i32, i32, vp]),
     "cs_allreduce_bucket": (i32, [vp, vp, i64, f32, i32, sz, i32, vp]),
     "cs_allreduce_bucket_local": (i32, [C.POINTER(vp), i32, C.POINTER(vp), i64, f32, i32, sz, i32, vp]),
     "cs_stage_h2d": (i32, [vp, vp, sz, vp]),

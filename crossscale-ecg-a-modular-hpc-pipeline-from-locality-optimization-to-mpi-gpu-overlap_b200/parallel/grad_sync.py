@@ -8,6 +8,11 @@ stream), so the collective of bucket *i* runs while autograd is still producing 
 in-flight bucket has its own barrier channel and arena region.  The collective itself is the in-kernel
 NVLink two-shot of ``csrc/cuda/fedavg.cu`` (``cs_allreduce_bucket``) — no NCCL on this path.
 ``finish()`` makes the compute stream wait for every bucket before the optimizer step.
+
+The same bucket pipeline also carries the FedAvg aggregation of large models: with ``fused_op`` set for one
+backward pass, a finished bucket launches ``cs_fedavg_bucket`` (optimizer step of the bucket + in-place two-shot
+aggregation + bf16 shadow, ``csrc/cuda/fedavg.cu``) instead of an all-reduce, so the aggregation of bucket *i* is on
+the wire while backward still computes bucket *i+1* (``backend="off"``: hooks only, no per-step all-reduce).
 """
 from __future__ import annotations
 
@@ -28,7 +33,9 @@ class GradSync:
                  comm: Optional[SymmetricComm] = None, backend: str = "kernel"):
         self.flat, self.wire_bf16 = flat, int(wire == "bf16")
         self.world = dist.get_world_size() if dist.is_initialized() else 1
-        self.backend = backend if self.world > 1 or backend == "kernel" else "none"
+        self.backend = backend if self.world > 1 or backend in ("kernel", "off") else "none"
+        self.fused_op = None          # callable(bucket_index, bucket, channel, side_stream): replaces the all-reduce for ONE backward
+        self.timeline = None          # set to a list: (bucket, ready, start, end) timing events of every launch
         dev = flat.flat.device
         # buckets in REVERSE parameter order (gradients arrive roughly last layer first); the arena must have been
         # built with ``align=4`` so every bucket boundary is 16-byte aligned and buckets are disjoint
@@ -45,7 +52,7 @@ class GradSync:
                 hi, cur, members = flat.offsets[i], 0, []
         lib = _lib.cuda_lib()
         self.channels = min(MAX_CHANNELS, max(1, len(self.buckets)))
-        self.region = max(int(lib.cs_fedavg_arena_bytes(b["hi_al"] - b["lo_al"], self.wire_bf16, self.world)) for b in self.buckets)
+        self.region = 0 if self.backend == "off" else max(int(lib.cs_fedavg_arena_bytes(b["hi_al"] - b["lo_al"], self.wire_bf16, self.world)) for b in self.buckets)
         self.region = (self.region + 255) // 256 * 256
         self.comm = comm
         if self.backend == "kernel":
@@ -69,7 +76,7 @@ class GradSync:
             j = self._owner[i]
             b = self.buckets[j]
             b["pending"] -= 1
-            if b["pending"] == 0 and not b.get("launched"):
+            if b["pending"] == 0 and not b.get("launched") and (self.fused_op is not None or self.backend != "off"):
                 self._launch(j)
         return hook
 
@@ -77,18 +84,28 @@ class GradSync:
         b = self.buckets[j]
         ch = j % self.channels
         side = self.streams[ch]
-        ready = torch.cuda.Event()
+        timed = self.timeline is not None
+        ready = torch.cuda.Event(enable_timing=timed)
         ready.record()                                     # gradients of this bucket are complete on the compute stream
         side.wait_event(ready)
+        if timed:
+            t0 = torch.cuda.Event(enable_timing=True)
+            t0.record(side)
         g = self.flat.grad[b["lo_al"]:b["hi_al"]]
         n = b["hi_al"] - b["lo_al"]
-        if self.backend == "kernel":
+        if self.fused_op is not None:
+            self.fused_op(j, b, ch, side)
+        elif self.backend == "kernel":
             _lib.check(_lib.cuda_lib().cs_allreduce_bucket(self.comm.handle, g.data_ptr(), n, 1.0 / self.world, self.wire_bf16,
                                                            ch * self.region, ch, side.cuda_stream), "cs_allreduce_bucket")
         elif self.backend == "nccl" and self.world > 1:
             with torch.cuda.stream(side):
                 dist.all_reduce(g)
                 g.mul_(1.0 / self.world)
+        if timed:
+            t1 = torch.cuda.Event(enable_timing=True)
+            t1.record(side)
+            self.timeline.append((j, ready, t0, t1))
         self.done_events[j].record(side)
         b["launched"] = True
         self.launches += 1
@@ -99,6 +116,6 @@ class GradSync:
         for j, b in enumerate(self.buckets):
             if b.get("launched"):
                 cur.wait_event(self.done_events[j])
-            elif b["pending"] != len(b["members"]):
+            elif b["pending"] not in ((0, len(b["members"])) if self.backend == "off" else (len(b["members"]),)):
                 raise RuntimeError(f"gradient bucket {j}: {b['pending']} of {len(b['members'])} gradients never arrived")
             b["pending"], b["launched"] = len(b["members"]), False

@@ -56,6 +56,10 @@ class SymmetricComm:
         _lib.check(_lib.cuda_lib().cs_comm_status(self._h, C.byref(out)), "cs_comm_status")
         return out.value
 
+    def set_timeout_ms(self, ms: int) -> None:
+        """how long an in-kernel cross-GPU flag wait may spin before it gives up (default 4000 ms)"""
+        _lib.check(_lib.cuda_lib().cs_comm_set_timeout_ms(self._h, int(ms)), "cs_comm_set_timeout_ms")
+
     def close(self) -> None:
         if self._h:
             torch.cuda.synchronize()
@@ -101,6 +105,9 @@ class LocalGroup:
             _lib.check(_lib.cuda_lib().cs_comm_status(self._arr[r], C.byref(out)), "cs_comm_status")
             worst = max(worst, out.value)
         return worst
+
+    def set_timeout_ms(self, ms: int) -> None:
+        _lib.check(_lib.cuda_lib().cs_comm_set_timeout_ms(self._arr[0], int(ms)), "cs_comm_set_timeout_ms")
 
     def close(self) -> None:
         if self._arr is not None and self._arr[0]:

@@ -64,12 +64,16 @@ int comm_barrier(cs_comm*, int, cudaStream_t);
 int comm_status(cs_comm*, int*);
 int comm_set_timeout_ms(cs_comm*, long long);
 int comm_clear_status(cs_comm*);
+int debug_fedavg_aggregate_alone(cs_comm*, float*, float*, long long, float, float*, cudaStream_t);
 size_t agg_arena_need(long long, int, int);
 int fedavg_aggregate(cs_comm*, float*, float*, long long, float, int, float, float*, size_t, int, float, cudaStream_t);
 int fedavg_aggregate_local(cs_comm**, int, float* const*, float* const*, long long, const float*, int, float,
                            float* const*, size_t, int, float, cudaStream_t);
 int fedavg_aggregate_inplace(cs_comm*, size_t, float*, long long, const float*, float, float*, int, cudaStream_t);
 int fedavg_aggregate_inplace_local(cs_comm**, int, size_t, float* const*, long long, const float*, float, float* const*, int, cudaStream_t);
+int fedavg_bucket(cs_comm*, size_t, const float*, float*, float*, void*, long long, const float*, float, float, float, float, float, int, int, int, cudaStream_t);
+int fedavg_bucket_local(cs_comm**, int, size_t, const float* const*, float* const*, float* const*, void* const*, long long, const float*, float, float,
+                        float, float, float, int, int, cudaStream_t);
 int fedavg_aggregate_nvls(cs_comm*, float*, void*, float*, long long, float, float, float, float*, int, cudaStream_t);
 void* comm_arena(cs_comm*, int);
 size_t comm_bytes(cs_comm*);
@@ -265,6 +269,10 @@ int cs_comm_barrier(cs_comm_t* c, int channel, cs_stream_t s) { return comm_barr
 int cs_comm_status(cs_comm_t* c, int* out) { return comm_status((cs_comm*)c, out); }
 int cs_comm_set_timeout_ms(cs_comm_t* c, long long ms) { return comm_set_timeout_ms((cs_comm*)c, ms); }
 int cs_comm_clear_status(cs_comm_t* c) { return comm_clear_status((cs_comm*)c); }
+/* debug: one emulated member aggregates alone (its peers never arrive): exercises the barrier time-out */
+int cs_debug_fedavg_aggregate_alone(cs_comm_t* member, float* local, float* prev, int64_t n, float weight, float* mom, cs_stream_t s) {
+    return debug_fedavg_aggregate_alone((cs_comm*)member, local, prev, n, weight, mom, ST(s));
+}
 size_t cs_fedavg_arena_bytes(int64_t n, int wire_bf16, int world) { return agg_arena_need(n, wire_bf16, world); }
 
 int cs_fedavg_aggregate(cs_comm_t* c, float* local, float* prev, int64_t n, float weight, int wire_bf16,
@@ -288,6 +296,18 @@ int cs_fedavg_aggregate_inplace_local(cs_comm_t** group, int world, size_t param
 int cs_fedavg_aggregate_nvls(cs_comm_t* c, float* local, void* multicast, float* prev, int64_t n, float prescale,
                              float post_scale, float server_lr, float* mom, int channel, cs_stream_t s) {
     return fedavg_aggregate_nvls((cs_comm*)c, local, multicast, prev, n, prescale, post_scale, server_lr, mom, channel, ST(s));
+}
+int cs_fedavg_bucket(cs_comm_t* c, size_t param_off, const float* grad, float* mom, float* prev, void* shadow_bf16, int64_t n,
+                     const float* weights, float lr, float momentum, float wd, float inv_scale, float server_lr, int do_sgd,
+                     int channel, int max_blocks, cs_stream_t s) {
+    return fedavg_bucket((cs_comm*)c, param_off, grad, mom, prev, shadow_bf16, n, weights, lr, momentum, wd, inv_scale, server_lr,
+                         do_sgd, channel, max_blocks, ST(s));
+}
+int cs_fedavg_bucket_local(cs_comm_t** group, int world, size_t param_off, const float* const* grad, float* const* mom,
+                           float* const* prev, void* const* shadow_bf16, int64_t n, const float* weights, float lr, float momentum,
+                           float wd, float inv_scale, float server_lr, int do_sgd, int channel, cs_stream_t s) {
+    return fedavg_bucket_local((cs_comm**)group, world, param_off, grad, mom, prev, shadow_bf16, n, weights, lr, momentum, wd,
+                               inv_scale, server_lr, do_sgd, channel, ST(s));
 }
 int cs_allreduce_bucket(cs_comm_t* c, float* grad, int64_t n, float scale, int wire_bf16, size_t arena_off,
                         int channel, cs_stream_t s) {

@@ -330,6 +330,134 @@ __global__ void __launch_bounds__(kCommThreads) fedavg_inplace_kernel(const Comm
 }
 
 // ------------------------------------------------------------------------------------------------
+// Bucket-fused FedAvg for large models (K7 "bucketed so it pipelines with the producing kernel").  One launch per
+// gradient bucket, issued on a side stream the moment the LAST local step's backward has produced that bucket:
+//   phase 0  this rank's SGD-momentum update of the bucket (the optimizer step of the last local step, in place in
+//            the symmetric arena) - the separate optimizer launch of that step disappears;
+//   barrier  every rank has updated this bucket;
+//   phase 1  in-place two-shot on the bucket: rank r reads slice r of every replica over NVLink, forms the weighted
+//            mean (+ server update) and stores it into slice r of EVERY replica;
+//   barrier  every push has landed;
+//   phase 2  bf16 shadow of the bucket (what the conv kernels read) - the separate full-model cast pass disappears.
+// While bucket i is on the wire the compute stream is still running backward for bucket i+1, so only the last
+// bucket's collective is exposed.  Work is partitioned like the in-place kernel: block b only ever consumes what
+// block b of a peer produced, so per-block flags suffice and no block waits on another block of its own GPU.
+// ------------------------------------------------------------------------------------------------
+struct BucketCall {
+    size_t param_off[kMaxRanks];       // byte offset of the bucket's parameters inside each (emulated) rank's arena
+    const float* grad[kMaxRanks];      // bucket-local pointers
+    float* mom[kMaxRanks];
+    float* prev[kMaxRanks];            // optional previous global model of the bucket (server_lr != 1; slice-local use)
+    void* shadow[kMaxRanks];           // optional bf16 copy of the bucket
+    float weights[kMaxRanks];
+    long long n;                       // multiple of 4
+    float lr, momentum, wd, server_lr, inv_scale;
+    int do_sgd, channel;
+};
+
+__global__ void __launch_bounds__(kCommThreads) fedavg_bucket_kernel(const CommDev* ctxs, BucketCall a) {
+    const int er = blockIdx.y;
+    const CommDev& c = ctxs[er];
+    const int P = c.world, b = blockIdx.x, nb = gridDim.x, T = blockDim.x, tid = threadIdx.x;
+    uint32_t* ep = c.epochs + (size_t)a.channel * kMaxBlocks + b;
+    const uint32_t e0 = *ep;
+    const long long n4 = a.n >> 2;
+    const long long gps = (n4 + P - 1) / P, gpb = (gps + nb - 1) / nb;
+    float4* mine = reinterpret_cast<float4*>(c.arena[c.rank] + a.param_off[er]);
+    float* prev = a.prev[er];
+    if (a.do_sgd) {                                            // phase 0: local optimizer step on every (slice, this block) piece
+        const float4* grad = reinterpret_cast<const float4*>(a.grad[er]);
+        float4* mom = reinterpret_cast<float4*>(a.mom[er]);
+        const float mu = a.momentum, wd = a.wd, lr = a.lr, is = a.inv_scale;
+        for (int s = 0; s < P; ++s) {
+            const long long g0 = s * gps + (long long)b * gpb;
+            long long g1 = g0 + gpb; if (g1 > (s + 1) * gps) g1 = (s + 1) * gps; if (g1 > n4) g1 = n4;
+            for (long long g = g0 + tid; g < g1; g += (long long)kU * T) {
+                float4 p[kU], m[kU], d[kU];
+#pragma unroll
+                for (int u = 0; u < kU; ++u) {
+                    const long long gi = g + (long long)u * T;
+                    if (gi < g1) { p[u] = mine[gi]; m[u] = mom[gi]; d[u] = __ldcs(grad + gi); }
+                }
+#pragma unroll
+                for (int u = 0; u < kU; ++u) {
+                    const long long gi = g + (long long)u * T;
+                    if (gi < g1) {
+                        m[u].x = mu * m[u].x + (d[u].x * is + wd * p[u].x); p[u].x -= lr * m[u].x;
+                        m[u].y = mu * m[u].y + (d[u].y * is + wd * p[u].y); p[u].y -= lr * m[u].y;
+                        m[u].z = mu * m[u].z + (d[u].z * is + wd * p[u].z); p[u].z -= lr * m[u].z;
+                        m[u].w = mu * m[u].w + (d[u].w * is + wd * p[u].w); p[u].w -= lr * m[u].w;
+                        mom[gi] = m[u]; mine[gi] = p[u];
+                    }
+                }
+            }
+        }
+    }
+    const bool ok = xgpu_barrier(c, a.channel, b, e0 + 1);     // every rank has stepped this bucket
+    if (ok) {
+        const int s = c.rank;
+        const long long g0 = s * gps + (long long)b * gpb;
+        long long g1 = g0 + gpb; if (g1 > (s + 1) * gps) g1 = (s + 1) * gps; if (g1 > n4) g1 = n4;
+        constexpr int U2 = 2;
+        for (long long g = g0 + tid; g < g1; g += (long long)U2 * T) {
+            float4 r[U2][kMaxRanks], q[U2];
+#pragma unroll
+            for (int u = 0; u < U2; ++u) {
+                const long long gi = g + (long long)u * T;
+#pragma unroll
+                for (int p = 0; p < kMaxRanks; ++p)
+                    if (p < P && gi < g1)
+                        r[u][p] = __ldcg(reinterpret_cast<const float4*>(c.arena[(c.rank + p) % P] + a.param_off[er]) + gi);
+                if (prev && gi < g1) q[u] = reinterpret_cast<const float4*>(prev)[gi];
+            }
+#pragma unroll
+            for (int u = 0; u < U2; ++u) {
+                const long long gi = g + (long long)u * T;
+                if (gi < g1) {
+                    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                    for (int p = 0; p < kMaxRanks; ++p)
+                        if (p < P) {
+                            const float w = a.weights[(c.rank + p) % P];
+                            acc.x = fmaf(w, r[u][p].x, acc.x); acc.y = fmaf(w, r[u][p].y, acc.y);
+                            acc.z = fmaf(w, r[u][p].z, acc.z); acc.w = fmaf(w, r[u][p].w, acc.w);
+                        }
+                    if (prev) {
+                        acc = make_float4(q[u].x + a.server_lr * (acc.x - q[u].x), q[u].y + a.server_lr * (acc.y - q[u].y),
+                                          q[u].z + a.server_lr * (acc.z - q[u].z), q[u].w + a.server_lr * (acc.w - q[u].w));
+                        reinterpret_cast<float4*>(prev)[gi] = acc;
+                    }
+                    for (int p = 0; p < P; ++p)
+                        reinterpret_cast<float4*>(c.arena[(c.rank + p) % P] + a.param_off[er])[gi] = acc;
+                }
+            }
+        }
+    }
+    if (ok) xgpu_barrier(c, a.channel, b, e0 + 2);             // every push has landed in my replica
+    if (a.shadow[er]) {                                        // phase 2: bf16 shadow of the whole bucket (local)
+        uint2* sh = reinterpret_cast<uint2*>(a.shadow[er]);
+        for (int s = 0; s < P; ++s) {
+            const long long g0 = s * gps + (long long)b * gpb;
+            long long g1 = g0 + gpb; if (g1 > (s + 1) * gps) g1 = (s + 1) * gps; if (g1 > n4) g1 = n4;
+            for (long long g = g0 + tid; g < g1; g += (long long)kU * T) {
+                float4 p[kU];
+#pragma unroll
+                for (int u = 0; u < kU; ++u) { const long long gi = g + (long long)u * T; if (gi < g1) p[u] = __ldcg(mine + gi); }
+#pragma unroll
+                for (int u = 0; u < kU; ++u) {
+                    const long long gi = g + (long long)u * T;
+                    if (gi < g1) {
+                        __nv_bfloat162 lo = __floats2bfloat162_rn(p[u].x, p[u].y), hi = __floats2bfloat162_rn(p[u].z, p[u].w);
+                        sh[gi] = make_uint2(*reinterpret_cast<uint32_t*>(&lo), *reinterpret_cast<uint32_t*>(&hi));
+                    }
+                }
+            }
+        }
+    }
+    if (threadIdx.x == 0) *ep = e0 + 2;
+}
+
+// ------------------------------------------------------------------------------------------------
 // NVLS variant of the in-place aggregation: the parameters live in a symmetric buffer that is also mapped
 // through an NVSwitch MULTICAST address.  Rank r pulls the switch-reduced slice r with
 // multimem.ld_reduce (the switch fetches and adds all replicas: N/P floats come in instead of (P-1)N/P),
@@ -592,6 +720,16 @@ int fedavg_aggregate(cs_comm* c, float* local, float* prev, long long n, float w
     return launch_agg(c->dev, 1, c->world, c->bytes, a, st);
 }
 
+// Test hook: launch ONE member of an emulated group on its own, so that its peers never arrive and the time-out path runs.
+int debug_fedavg_aggregate_alone(cs_comm* member, float* local, float* prev, long long n, float weight, float* mom,
+                                 cudaStream_t st) {
+    CS_REQUIRE(member && member->emulated, "debug_aggregate_alone: needs a member of an emulated group");
+    AggCall a; memset(&a, 0, sizeof(a));
+    a.local[0] = local; a.prev[0] = prev; a.mom[0] = mom; a.weight[0] = weight;
+    a.n = n; a.server_lr = 1.0f; a.post_scale = 1.0f; a.wire_bf16 = 0; a.channel = 0; a.arena_off = 0;
+    return launch_agg(member->dev, 1, member->world, member->bytes, a, st);
+}
+
 int fedavg_aggregate_local(cs_comm** g, int world, float* const* local, float* const* prev, long long n,
                            const float* weights, int wire_bf16, float server_lr, float* const* mom,
                            size_t arena_off, int channel, float post_scale, cudaStream_t st) {
@@ -643,6 +781,52 @@ int fedavg_aggregate_inplace_local(cs_comm** g, int world, size_t param_off, flo
     }
     a.n = n; a.server_lr = server_lr; a.channel = channel;
     return launch_inplace(g[0]->group_dev, world, a, st);
+}
+
+static int launch_bucket(const CommDev* ctxs, int ranks, const BucketCall& a, int max_blocks, cudaStream_t st) {
+    CS_REQUIRE(a.n > 0 && a.n % 4 == 0, "fedavg_bucket: n must be a positive multiple of 4");
+    CS_REQUIRE(a.channel >= 0 && a.channel < kChannels, "fedavg_bucket: bad channel");
+    int nb = pick_blocks(a.n, false);
+    if (max_blocks > 0 && nb > max_blocks) nb = max_blocks;
+    const void* fn = (const void*)fedavg_bucket_kernel;
+    if (ranks > 1) {
+        int per_sm = 1;
+        CS_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, kCommThreads, 0));
+        int cap = (num_sms() * (per_sm < 1 ? 1 : per_sm)) / ranks;
+        if (nb > cap) nb = cap < 1 ? 1 : cap;
+    }
+    dim3 grid(nb, ranks), block(kCommThreads);
+    void* args[] = {(void*)&ctxs, (void*)&a};
+    if (ranks > 1) CS_CUDA_OK(cudaLaunchCooperativeKernel(fn, grid, block, args, 0, st));
+    else CS_CUDA_OK(cudaLaunchKernel(fn, grid, block, args, 0, st));
+    return CS_OK;
+}
+
+int fedavg_bucket(cs_comm* c, size_t param_off, const float* grad, float* mom, float* prev, void* shadow, long long n,
+                  const float* weights, float lr, float momentum, float wd, float inv_scale, float server_lr, int do_sgd,
+                  int channel, int max_blocks, cudaStream_t st) {
+    CS_REQUIRE(c && !c->emulated, "fedavg_bucket: use the *_local entry point for emulated groups");
+    CS_REQUIRE(param_off % 16 == 0 && param_off + (size_t)n * 4 <= c->bytes, "fedavg_bucket: the bucket must lie inside the arena");
+    CS_REQUIRE(!do_sgd || (grad && mom), "fedavg_bucket: the fused optimizer step needs grad and momentum");
+    BucketCall a; memset(&a, 0, sizeof(a));
+    a.param_off[0] = param_off; a.grad[0] = grad; a.mom[0] = mom; a.prev[0] = prev; a.shadow[0] = shadow;
+    for (int r = 0; r < c->world; ++r) a.weights[r] = weights[r];
+    a.n = n; a.lr = lr; a.momentum = momentum; a.wd = wd; a.inv_scale = inv_scale; a.server_lr = server_lr; a.do_sgd = do_sgd; a.channel = channel;
+    return launch_bucket(c->dev, 1, a, max_blocks, st);
+}
+
+int fedavg_bucket_local(cs_comm** g, int world, size_t param_off, const float* const* grad, float* const* mom, float* const* prev,
+                        void* const* shadow, long long n, const float* weights, float lr, float momentum, float wd, float inv_scale,
+                        float server_lr, int do_sgd, int channel, cudaStream_t st) {
+    CS_REQUIRE(g && g[0] && g[0]->emulated && g[0]->world == world, "fedavg_bucket_local: not an emulated group");
+    CS_REQUIRE(param_off % 16 == 0 && param_off + (size_t)n * 4 <= g[0]->bytes, "fedavg_bucket: the bucket must lie inside the arena");
+    BucketCall a; memset(&a, 0, sizeof(a));
+    for (int r = 0; r < world; ++r) {
+        a.param_off[r] = param_off; a.grad[r] = grad ? grad[r] : nullptr; a.mom[r] = mom ? mom[r] : nullptr;
+        a.prev[r] = prev ? prev[r] : nullptr; a.shadow[r] = shadow ? shadow[r] : nullptr; a.weights[r] = weights[r];
+    }
+    a.n = n; a.lr = lr; a.momentum = momentum; a.wd = wd; a.inv_scale = inv_scale; a.server_lr = server_lr; a.do_sgd = do_sgd; a.channel = channel;
+    return launch_bucket(g[0]->group_dev, world, a, 0, st);
 }
 
 int fedavg_aggregate_nvls(cs_comm* c, float* local, void* mc, float* prev, long long n, float prescale, float post_scale,

@@ -23,9 +23,16 @@
 //     array and corrupt each other's gradients.  Serialise them on one stream, or give concurrent
 //     trainers their own buffer through cs_tiny_ecg_train_step.
 //   * Nothing here calls cudaMalloc, cudaFree or any allocating library routine.
+//   * This is the slower of the two entry points when steps are issued back to back: the cudaMemsetAsync that
+//     clears the array sits between consecutive step kernels, so the programmatic dependent launch that lets
+//     cs_tiny_ecg_train_step start its prologue under the previous step's tail never engages here.
+//   * The per-device address cache is a table of atomics: two host threads that make their first call on the
+//     same device at the same time both look the address up and store the same value.
 #include "tiny_ecg.cuh"
 
 #include <string.h>
+
+#include <atomic>
 
 namespace cs {
 
@@ -34,23 +41,35 @@ static __device__ __align__(256) float g_tiny_static_scratch[CS_TINY_NOALLOC_SCR
 // The symbol above is only a host-side handle; kernels need its device address.  One look-up per
 // device, done with that device current.
 static int static_scratch_ptr(float** out) {
-    static float* ptr[64] = {};
+    static std::atomic<float*> ptr[64];
     int dev = 0;
     CS_CUDA_OK(cudaGetDevice(&dev));
     CS_REQUIRE(dev >= 0 && dev < 64, "noalloc: device ordinal %d out of range", dev);
-    if (ptr[dev] == nullptr) {
+    float* cached = ptr[dev].load(std::memory_order_acquire);
+    if (cached == nullptr) {
         void* p = nullptr;
         CS_CUDA_OK(cudaGetSymbolAddress(&p, g_tiny_static_scratch));
         CS_REQUIRE(p != nullptr, "noalloc: cudaGetSymbolAddress returned a null address");
-        ptr[dev] = static_cast<float*>(p);
+        cached = static_cast<float*>(p);
+        ptr[dev].store(cached, std::memory_order_release);
     }
-    *out = ptr[dev];
+    *out = cached;
     return CS_OK;
 }
 
 }  // namespace cs
 
 using namespace cs;
+
+// Test hook: overwrite the built-in array with NaNs on `stream`, as if a previous call had been torn down half way.
+// The next cs_tiny_ecg_train_step_noalloc must still produce the right update (it clears what it uses first).
+extern "C" int cs_debug_noalloc_poison(cs_stream_t stream) {
+    float* scratch = nullptr;
+    int rc = static_scratch_ptr(&scratch);
+    if (rc != CS_OK) return rc;
+    CS_CUDA_OK(cudaMemsetAsync(scratch, 0xFF, sizeof(float) * CS_TINY_NOALLOC_SCRATCH_FLOATS, (cudaStream_t)stream));
+    return CS_OK;
+}
 
 extern "C" int cs_tiny_ecg_train_step_noalloc(const void* x, const int64_t* y, const int64_t* idx, int x_bf16, int B,
                                               int L, int C, float* params, float* mom, int32_t* ctrl, float* fstate,

@@ -622,13 +622,12 @@ size_t tiny_umma_scratch_floats() { return (size_t)kScratchReps * kScratchStride
 size_t tiny_umma_smem_bytes(int L, int C) { return L <= 512 ? USmem<4>::TOTAL : USmem<8>::TOTAL; }
 
 bool tiny_umma_supported(int L, int C) {
-    static int sm100 = -1;
-    if (sm100 < 0) {
-        int dev = 0, major = 0;
-        sm100 = (cudaGetDevice(&dev) == cudaSuccess &&
-                 cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev) == cudaSuccess && major == 10) ? 1 : 0;
-    }
-    return sm100 == 1 && L >= 8 && L <= 1024 && C >= 1 && C <= kTinyMaxC;
+    static int sm100[64] = {};                 // per device: 0 unknown, 1 yes, 2 no
+    int dev = 0, major = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return false;
+    if (sm100[dev] == 0)
+        sm100[dev] = (cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev) == cudaSuccess && major == 10) ? 1 : 2;
+    return sm100[dev] == 1 && L >= 8 && L <= 1024 && C >= 1 && C <= kTinyMaxC;
 }
 
 }  // namespace cs

@@ -359,6 +359,23 @@ int cs_fedavg_aggregate_nvls(cs_comm_t* c, float* local, void* multicast, float*
                              float prescale, float post_scale, float server_lr, float* mom,
                              int channel, cs_stream_t stream);
 
+/* K7 bucketed: optimizer step + in-place FedAvg + bf16 shadow of ONE gradient bucket in one launch, meant to be issued on a
+ * side stream as soon as the round's last backward has produced the bucket, so the aggregation of bucket i crosses NVLink
+ * while backward still computes bucket i+1.  ref: everything in comm_ms is exposed in the reference
+ * (TRUE_FL_M3/part3_fedavg_overlap_mpi_gpu.py:188-190,209-214: Allreduce only after the last step's optimizer.step()).
+ * The bucket's parameters live in the symmetric arena at byte offset param_off (same offset on every rank).
+ *   do_sgd != 0: buf = momentum*buf + (inv_scale*grad + wd*p); p -= lr*buf   on the whole bucket (grad, mom: bucket-local
+ *   pointers), then barrier, then rank r forms sum_j weights[j]*p_j (+ server update against prev when prev != NULL) on
+ *   slice r and stores it into slice r of every replica, barrier, then shadow_bf16 (optional) = bf16(bucket).
+ * max_blocks > 0 caps the CTAs of the launch (it shares the GPU with backward). */
+int cs_fedavg_bucket(cs_comm_t* c, size_t param_off, const float* grad, float* mom, float* prev, void* shadow_bf16,
+                     int64_t n, const float* weights /* host, world floats */, float lr, float momentum, float wd,
+                     float inv_scale, float server_lr, int do_sgd, int channel, int max_blocks, cs_stream_t stream);
+int cs_fedavg_bucket_local(cs_comm_t** group, int world, size_t param_off, const float* const* grad, float* const* mom,
+                           float* const* prev, void* const* shadow_bf16, int64_t n, const float* weights, float lr,
+                           float momentum, float wd, float inv_scale, float server_lr, int do_sgd, int channel,
+                           cs_stream_t stream);
+
 /* K8: gradient all-reduce of one bucket, in place: grad <- scale * sum_ranks grad  (fp32 [n]).
  * `arena_off` / `channel` let several buckets be in flight on different streams. */
 int cs_allreduce_bucket(cs_comm_t* c, float* grad, int64_t n, float scale, int wire_bf16,

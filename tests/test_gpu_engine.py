@@ -68,3 +68,37 @@ def test_pseudo_fl_engines_gpu(synth_shards):
     r1 = run_overlap_gpu(TinyECG(2).to(dev), it, dev, 20, 0, 128, 1, x, y)
     assert r0["config"] == "G0_baseline_GPU_CACHE" and r1["config"] == "G1_overlap_amp"
     assert r0["samples_per_s"] > 0 and r1["samples_per_s"] > 0 and r0["steps"] == 20
+
+
+@pytest.mark.parametrize("graph", [False, True])
+def test_bucket_fused_round_matches_separate_kernels_single_gpu(graph):
+    """KernelLocalTrainer: a round whose last backward launches per-bucket {optimizer step + in-place aggregation + bf16
+    shadow} kernels on side streams ends where the round with separate SGD / aggregation / shadow-cast kernels ends
+    (one client: the aggregation is the identity, so this checks the optimizer step, the hooks and the shadow)."""
+    import torch
+    from crossscale.data.synth import make_mitbih_like_beats
+    from crossscale.fl.engine import FedAvgRunner
+    from crossscale.models.resnet1d_wide import resnet1d_small
+    dev = torch.device("cuda", 0)
+    x, y = make_mitbih_like_beats(512, 360, 5, seed=3)
+    x, y = torch.from_numpy(x).to(dev), torch.from_numpy(y).to(dev)
+    finals, launches = {}, {}
+    for fused in (True, False):
+        torch.manual_seed(0)
+        model = resnet1d_small(5).to(dev)
+        gen = torch.Generator(device="cuda").manual_seed(77)
+        r = FedAvgRunner(model, dev, x, y, 32, 3, "G1", amp="bf16", generator=gen, model_name="resnet1d_small", inplace="on",
+                         fuse_bucket_agg=fused, use_graph=graph, bucket_bytes=8 << 10)
+        assert r.fuse_bucket_agg == fused
+        for rnd in range(4):
+            r.run_round(rnd)
+        finals[fused] = r.flat.clone()
+        launches[fused] = r.agg.launches
+        assert torch.equal(r.trainer.shadow, r.flat.to(torch.bfloat16))
+        assert r.agg.comm.status() == 0
+        if fused:
+            assert len(r.trainer.sync.buckets) >= 2
+        r.close()
+    assert launches[True] > launches[False]
+    rel = float((finals[True] - finals[False]).norm() / finals[False].norm())
+    assert rel < 2e-2, rel

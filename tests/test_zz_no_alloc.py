@@ -92,3 +92,40 @@ def test_noalloc_rejects_more_classes_than_the_array_holds():
     assert rc != 0
     msg = lib.cs_last_error().decode()
     assert "9 classes" in msg and "7168" in msg
+
+
+@pytest.mark.parametrize("amp", [0, 1])
+def test_noalloc_step_clears_what_an_earlier_caller_left_in_the_array(amp):
+    """The built-in array outlives every call.  Fill it with NaNs (what a torn-down caller, or a step with more
+    classes, may leave) and check that the next step still matches the regular entry point: the entry point
+    clears the part it uses before it launches."""
+    lib = _lib()
+    lib.cs_debug_noalloc_poison.restype = i32
+    lib.cs_debug_noalloc_poison.argtypes = [vp]
+    dev = torch.device("cuda", 0)
+    torch.cuda.set_device(dev)
+    torch.manual_seed(7)
+    ncls, batch, length = 2, 64, 500
+    nparam = 1424 + 17 * ncls
+    params0 = torch.nn.functional.pad(torch.randn(nparam, device=dev) * 0.2, (0, (-nparam) % 4))
+    data = torch.randn(512, length, device=dev)
+    labels = torch.randint(0, ncls, (512,), device=dev)
+    ref, new = _state(params0, dev), _state(params0, dev)
+    ref["fstate"][1] = new["fstate"][1] = 1.0
+    scratch = torch.zeros(int(lib.cs_tiny_ecg_scratch_floats(ncls)), device=dev)
+    stream = torch.cuda.current_stream().cuda_stream
+    hyper = (0.05, 0.9, 0.0, amp, 0, 2.0, 0.5, 2000)
+    idx = torch.randint(0, 512, (batch,), device=dev)
+    assert lib.cs_debug_noalloc_poison(stream) == 0, lib.cs_last_error()
+    rc = lib.cs_tiny_ecg_train_step(data.data_ptr(), labels.data_ptr(), idx.data_ptr(), 0, batch, length, ncls,
+                                    ref["params"].data_ptr(), ref["mom"].data_ptr(), scratch.data_ptr(),
+                                    ref["ctrl"].data_ptr(), ref["fstate"].data_ptr(), *hyper, stream)
+    assert rc == 0, lib.cs_last_error()
+    rc = lib.cs_tiny_ecg_train_step_noalloc(data.data_ptr(), labels.data_ptr(), idx.data_ptr(), 0, batch, length, ncls,
+                                            new["params"].data_ptr(), new["mom"].data_ptr(), new["ctrl"].data_ptr(),
+                                            new["fstate"].data_ptr(), *hyper, stream)
+    assert rc == 0, lib.cs_last_error()
+    torch.cuda.synchronize()
+    assert torch.isfinite(new["params"]).all() and int(new["ctrl"][3]) == 0      # no skipped step: nothing non-finite got in
+    torch.testing.assert_close(new["params"], ref["params"], rtol=1e-4, atol=1e-6)
+    torch.testing.assert_close(new["mom"], ref["mom"], rtol=1e-4, atol=1e-6)
