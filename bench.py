@@ -43,6 +43,7 @@ def parse():
     ap.add_argument("--num-windows", type=int, default=NUM_WINDOWS)
     ap.add_argument("--trace-e2e", action="store_true", help="per-rank timing breakdown of the staged rounds on stderr")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-resnet", action="store_true", help="skip the widened ResNet-1D FedAvg block (BASELINE.json config 5)")
     ap.add_argument("--no-arms", action="store_true", help="skip the extra fp16+scaler / fp32 arms measured after the headline")
     ap.add_argument("--windows", type=int, default=5, help="timed windows of --steps rounds each (value = median)")
     return ap.parse_args()
@@ -269,6 +270,18 @@ def run_ours(args):
             r2.close()
     clocks = sampler.stop()
 
+    # ---- BASELINE.json config 5: widened ResNet-1D FedAvg (aggregation-bandwidth stress), a few rounds ------------------
+    resnet = None
+    if not args.no_resnet:
+        import importlib.util
+        spec = importlib.util.spec_from_file_location("cs_resnet_fedavg", os.path.join(REPO, "bench", "resnet_fedavg.py"))
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+        try:
+            resnet = mod.measure(rank, world, device, rounds=5, local_steps=2, batch=64)
+        except Exception as e:                               # the headline must survive a failure of the side measurement
+            resnet = {"error": f"{type(e).__name__}: {e}"[:300]}
+
     if rank == 0:
         base = None
         try:
@@ -307,6 +320,8 @@ def run_ours(args):
             out["agg_max_abs_err"] = agg_err
         if arms:
             out["arms"] = arms
+        if resnet is not None:
+            out["resnet"] = resnet
         if e2e is not None:
             out["e2e"] = e2e
         emit(out)

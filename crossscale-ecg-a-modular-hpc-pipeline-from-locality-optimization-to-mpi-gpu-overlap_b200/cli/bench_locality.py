@@ -8,6 +8,13 @@ reference (``:111-116``) — except that A0 really samples randomly and A1..A3 c
 reference the sampler is a global flag, so A0 == A1).  ``--contiguous/--random`` still
 forces one sampler for every config when given explicitly.  Output: ``results/part1_locality_results.csv``
 (+ PNGs when matplotlib is installed).
+
+On a CUDA device one more row per batch size is measured, **A5_b200_staged_fused**: the B200-native answer to the
+reference's "pinned + non-blocking" idea.  Windows live in pinned host memory as bf16 (``PinnedShardStore``), blocks of
+``--a5-steps`` batches go host->device with ``cudaMemcpyAsync`` on a copy stream into a double-buffered slot
+(``H2DStager``) while the previous block trains, and a block's steps are ONE launch of the persistent fused kernel
+(``cs_tiny_ecg_train_round``).  Its ``h2d_ms`` is the copy's own duration per step (it overlaps compute), ``step_ms``
+the wall time per step, ``samples_per_s = B / step_ms``.
 """
 from __future__ import annotations
 
@@ -82,6 +89,68 @@ def measure_step(dl, device: torch.device, non_blocking: bool, iters: int = 50, 
                 samples_per_s=(n / iters) / (step_ms / 1e3))
 
 
+def measure_a5(device: torch.device, batch: int, iters: int, num_classes: int, dataset: str, num_windows: int,
+               steps_per_block: int = 10, amp: str = "bf16") -> dict:
+    """Pinned store -> copy-stream staging -> fused kernels; wall-clock per step with the copy overlapped."""
+    import numpy as np
+    from ..data.staging import BlockSampler, H2DStager, PinnedShardStore
+    from ..data.synth import make_mitbih_like_beats, make_synth_windows
+    from ..models import TinyECG
+    from ..ops import tiny_ecg as tk
+    if dataset == "mitbih":
+        x, y = make_mitbih_like_beats(num_windows, 360, num_classes, 1337)
+    else:
+        x, y = make_synth_windows(num_windows, 500, 1337), np.zeros(num_windows, dtype=np.int64)
+    dt = torch.bfloat16 if amp == "bf16" else torch.float32
+    store = PinnedShardStore([], dtype=dt, x=torch.from_numpy(np.ascontiguousarray(x, dtype=np.float32)),
+                             y=torch.from_numpy(np.ascontiguousarray(y, dtype=np.int64)))
+    rows = steps_per_block * batch
+    stager, sampler = H2DStager(rows, store.l, dt, device), BlockSampler(store.n, rows, seed=0)
+    model = TinyECG(num_classes).to(device)
+    st = tk.TinyTrainState(model.flatten_parameters().flat, num_classes, lr=1e-2, momentum=0.0, amp=tk.AMP_BY_NAME[amp])
+    use_round = st.round_supported() and tk.round_kernel_available()
+    blocks = max(2, (iters + steps_per_block - 1) // steps_per_block)
+    t_data = 0.0
+
+    def stage(slot):
+        nonlocal t_data
+        t0 = time.perf_counter()
+        hx, hy = store.block(sampler.next_start(), rows)
+        t_data += (time.perf_counter() - t0) * 1e3
+        stager.stage(slot, hx, hy)
+
+    def train(xb, yb):
+        if use_round:
+            st.round(xb, yb, steps_per_block, batch, sample_mode=tk.SAMPLE_ROWS)
+        else:
+            for s_ in range(steps_per_block):
+                st.step(xb[s_ * batch:(s_ + 1) * batch], yb[s_ * batch:(s_ + 1) * batch], None, batch=batch)
+
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    slot, wall = 0, 0.0
+    stage(0)
+    for n_blocks in (3, blocks):                              # warm-up, then the timed blocks
+        torch.cuda.synchronize()
+        t_data, stager.trace = 0.0, []
+        t0 = time.perf_counter()
+        ev[0].record()
+        for _ in range(n_blocks):
+            xb, yb = stager.acquire(slot)
+            stage(slot ^ 1)                                  # next block's copy runs under this block's compute
+            train(xb, yb)
+            stager.release(slot)
+            slot ^= 1
+        ev[1].record()
+        torch.cuda.synchronize()
+        wall = (time.perf_counter() - t0) * 1e3
+    st.check_errors()
+    steps = blocks * steps_per_block
+    copy_ms = sum(a.elapsed_time(b) for a, b in stager.trace) / max(1, len(stager.trace)) / steps_per_block
+    step_ms = max(wall, ev[0].elapsed_time(ev[1])) / steps
+    return dict(data_ms=t_data / steps, h2d_ms=copy_ms, compute_ms=ev[0].elapsed_time(ev[1]) / steps, step_ms=step_ms,
+                samples_per_s=batch / (step_ms / 1e3))
+
+
 def build_parser() -> argparse.ArgumentParser:
     ap = argparse.ArgumentParser()
     ap.add_argument("--dataset", choices=["mitbih", "synthetic"], default="mitbih")
@@ -93,6 +162,8 @@ def build_parser() -> argparse.ArgumentParser:
     ap.add_argument("--random", dest="contiguous", action="store_const", const=False)
     ap.add_argument("--results-dir", type=str, default="results")
     ap.add_argument("--num-windows", type=int, default=20000)
+    ap.add_argument("--a5-steps", type=int, default=10, help="batches per staged block of the A5 row")
+    ap.add_argument("--no-a5", action="store_true", help="skip the B200-native A5 row")
     return ap
 
 
@@ -115,6 +186,16 @@ def main(argv=None):
             print(f"[{name}] bs={bs}: {stats['samples_per_s']:,.0f} samples/s "
                   f"(data {stats['data_ms']:.2f} h2d {stats['h2d_ms']:.2f} compute {stats['compute_ms']:.2f} ms)")
             del dl
+        if device.type == "cuda" and not args.no_a5:
+            from ..ops import tiny_ecg as tk
+            if tk.use_kernels():
+                stats = measure_a5(device, bs, args.iters, ncls, args.dataset, max(args.num_windows, 2 * args.a5_steps * bs),
+                                   args.a5_steps)
+                rows.append(dict(config="A5_b200_staged_fused", batch_size=bs, pin_memory=True, contiguous=True,
+                                 non_blocking=True, **stats))
+                print(f"[A5_b200_staged_fused] bs={bs}: {stats['samples_per_s']:,.0f} samples/s "
+                      f"(data {stats['data_ms']:.3f} h2d {stats['h2d_ms']:.3f} [overlapped] device {stats['compute_ms']:.3f} "
+                      f"wall {stats['step_ms']:.3f} ms/step)")
     path = os.path.join(args.results_dir, "part1_locality_results.csv")
     if os.path.exists(path):
         os.remove(path)
