@@ -54,6 +54,7 @@ def main():
         tr = KernelLocalTrainer(m, dev, sync_grads=False, use_graph=False, bucket_bytes=int(a.bucket_mb * (1 << 20)))
         if mode != "off":
             tr.sync = GradSync(tr.flat, bucket_bytes=int(a.bucket_mb * (1 << 20)), backend=mode)
+            out["kernel_max_blocks"] = getattr(tr.sync, "max_blocks", None) if mode == "kernel" else out.get("kernel_max_blocks")
         return tr
 
     def step_ms(tr):

@@ -170,7 +170,8 @@ class KernelLocalTrainer:
         self._fused = None            # set by enable_fused_aggregation: the round's last step ends in the bucketed FedAvg
         self._graph_f, self._warm_f = None, 0
 
-    fused_max_blocks = 48             # CTAs per bucket launch: enough to fill NVLink, few enough to leave backward its SMs
+    import os as _os
+    fused_max_blocks = int(_os.environ.get("CS_BUCKET_BLOCKS", "8"))   # CTAs per bucket launch: they share the GPU with backward
 
     def enable_fused_aggregation(self, agg, prev: Optional[torch.Tensor]) -> bool:
         """Let the LAST local step of a round carry the aggregation: each gradient bucket, as soon as backward has

@@ -88,6 +88,15 @@ class FlatParams:
             p.data = new_flat[off:off + p.numel()].view_as(p)
 
 
+    def rebind_grad(self, new_grad: torch.Tensor) -> None:
+        """Point every parameter's gradient at ``new_grad`` (a peer-mapped arena: the bucketed gradient all-reduce then
+        works in place on it, without staging copies)."""
+        new_grad[: self.grad.numel()].copy_(self.grad)
+        self.grad = new_grad
+        for p, off in zip(self.params, self.offsets):
+            p.grad = new_grad[off:off + p.numel()].view_as(p)
+
+
 class TinyECG(nn.Module):
     def __init__(self, num_classes: int = 2):
         super().__init__()

@@ -77,6 +77,7 @@ _CUDA_SIGS = {
     "cs_comm_status": (i32, [vp, C.POINTER(i32)]),
     "cs_comm_set_timeout_ms": (i32, [vp, C.c_longlong]),
     "cs_comm_clear_status": (i32, [vp]),
+    "cs_comm_set_max_blocks": (i32, [vp, i32]),
     "cs_debug_fedavg_aggregate_alone": (i32, [vp, vp, vp, i64, f32, vp, vp]),
     "cs_comm_barrier": (i32, [vp, i32, vp]),
     "cs_fedavg_arena_bytes": (sz, [i64, i32, i32]),

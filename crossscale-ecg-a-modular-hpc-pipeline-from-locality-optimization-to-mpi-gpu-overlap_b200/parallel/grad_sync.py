@@ -30,7 +30,8 @@ MAX_CHANNELS = 8
 
 class GradSync:
     def __init__(self, flat: FlatParams, bucket_bytes: int = 4 << 20, wire: str = "fp32",
-                 comm: Optional[SymmetricComm] = None, backend: str = "kernel"):
+                 comm: Optional[SymmetricComm] = None, backend: str = "kernel", max_blocks: Optional[int] = None,
+                 inplace: bool = True):
         self.flat, self.wire_bf16 = flat, int(wire == "bf16")
         self.world = dist.get_world_size() if dist.is_initialized() else 1
         self.backend = backend if self.world > 1 or backend in ("kernel", "off") else "none"
@@ -55,12 +56,24 @@ class GradSync:
         self.region = 0 if self.backend == "off" else max(int(lib.cs_fedavg_arena_bytes(b["hi_al"] - b["lo_al"], self.wire_bf16, self.world)) for b in self.buckets)
         self.region = (self.region + 255) // 256 * 256
         self.comm = comm
+        # fp32 wire: the gradient arena itself moves into peer-mapped memory and every bucket is reduced IN PLACE (rank r
+        # averages slice r of all replicas over NVLink and stores it back into every replica): one pass over HBM instead
+        # of the staged kernel's encode / reduce / apply passes, which compete with backward for memory bandwidth
+        self.inplace = bool(self.backend == "kernel" and not self.wire_bf16 and inplace)
         if self.backend == "kernel":
-            need = self.region * self.channels
+            need = flat.grad.numel() * 4 if self.inplace else self.region * self.channels
             if self.comm is None:
                 self.comm = SymmetricComm(need)
             elif self.comm.arena_bytes < need:
                 raise ValueError("grad-sync arena too small")
+            # these collectives run under backward and their CTAs spin at the cross-GPU barriers: keep them few
+            import os
+            self.max_blocks = int(os.environ.get("CS_GRADSYNC_BLOCKS", "16")) if max_blocks is None else int(max_blocks)
+            _lib.check(lib.cs_comm_set_max_blocks(self.comm.handle, self.max_blocks), "cs_comm_set_max_blocks")
+            if self.inplace:
+                import ctypes as C
+                flat.rebind_grad(self.comm.arena_tensor(flat.grad.numel()))
+                self._mean_w = (C.c_float * self.world)(*[1.0 / self.world] * self.world)
         self.streams = [torch.cuda.Stream(device=dev) for _ in range(self.channels)]
         self.done_events = [torch.cuda.Event() for _ in self.buckets]
         self.launches = 0
@@ -95,6 +108,9 @@ class GradSync:
         n = b["hi_al"] - b["lo_al"]
         if self.fused_op is not None:
             self.fused_op(j, b, ch, side)
+        elif self.backend == "kernel" and self.inplace:
+            _lib.check(_lib.cuda_lib().cs_fedavg_aggregate_inplace(self.comm.handle, b["lo_al"] * 4, None, n, self._mean_w, 1.0, None,
+                                                                   ch, side.cuda_stream), "cs_fedavg_aggregate_inplace")
         elif self.backend == "kernel":
             _lib.check(_lib.cuda_lib().cs_allreduce_bucket(self.comm.handle, g.data_ptr(), n, 1.0 / self.world, self.wire_bf16,
                                                            ch * self.region, ch, side.cuda_stream), "cs_allreduce_bucket")

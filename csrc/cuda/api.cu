@@ -64,6 +64,7 @@ int comm_barrier(cs_comm*, int, cudaStream_t);
 int comm_status(cs_comm*, int*);
 int comm_set_timeout_ms(cs_comm*, long long);
 int comm_clear_status(cs_comm*);
+int comm_set_max_blocks(cs_comm*, int);
 int debug_fedavg_aggregate_alone(cs_comm*, float*, float*, long long, float, float*, cudaStream_t);
 size_t agg_arena_need(long long, int, int);
 int fedavg_aggregate(cs_comm*, float*, float*, long long, float, int, float, float*, size_t, int, float, cudaStream_t);
@@ -269,6 +270,7 @@ int cs_comm_barrier(cs_comm_t* c, int channel, cs_stream_t s) { return comm_barr
 int cs_comm_status(cs_comm_t* c, int* out) { return comm_status((cs_comm*)c, out); }
 int cs_comm_set_timeout_ms(cs_comm_t* c, long long ms) { return comm_set_timeout_ms((cs_comm*)c, ms); }
 int cs_comm_clear_status(cs_comm_t* c) { return comm_clear_status((cs_comm*)c); }
+int cs_comm_set_max_blocks(cs_comm_t* c, int n) { return comm_set_max_blocks((cs_comm*)c, n); }
 /* debug: one emulated member aggregates alone (its peers never arrive): exercises the barrier time-out */
 int cs_debug_fedavg_aggregate_alone(cs_comm_t* member, float* local, float* prev, int64_t n, float weight, float* mom, cs_stream_t s) {
     return debug_fedavg_aggregate_alone((cs_comm*)member, local, prev, n, weight, mom, ST(s));

@@ -35,6 +35,7 @@ struct cs_comm {
     int* status = nullptr;            // device alias of status_host
     int* status_host = nullptr;       // pinned + mapped: the host reads it without a copy or a synchronisation of its own
     unsigned long long timeout_ns = 4000000000ull;
+    int max_blocks = 0;               // > 0: cap on the CTAs of every collective launched on this communicator (same on all ranks)
     void* peer_arena[cs::kMaxRanks] = {};
     uint32_t* peer_signals[cs::kMaxRanks] = {};
     bool opened[cs::kMaxRanks] = {};

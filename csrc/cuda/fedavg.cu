@@ -683,7 +683,7 @@ size_t agg_arena_need(long long n, int wire_bf16, int world) {
 }
 
 // Launch for a real rank (ranks = 1 context) or for an emulated group (ranks = world contexts).
-static int launch_agg(const CommDev* ctxs, int ranks, int world, size_t arena_bytes, const AggCall& a, cudaStream_t st) {
+static int launch_agg(const CommDev* ctxs, int ranks, int world, size_t arena_bytes, const AggCall& a, cudaStream_t st, int max_blocks = 0) {
     CS_REQUIRE(a.n > 0, "aggregate: n must be positive");
     CS_REQUIRE(a.channel >= 0 && a.channel < kChannels, "aggregate: channel %d out of range", a.channel);
     CS_REQUIRE(a.arena_off % 16 == 0, "aggregate: arena offset must be 16-byte aligned");
@@ -692,6 +692,7 @@ static int launch_agg(const CommDev* ctxs, int ranks, int world, size_t arena_by
                agg_arena_need(a.n, a.wire_bf16, world), a.arena_off, arena_bytes);
     const bool oneshot = a.n <= kOneShotMaxElems;
     int nb = pick_blocks(a.n, oneshot);
+    if (max_blocks > 0 && nb > max_blocks) nb = max_blocks;    // (the partition depends on nb: every rank must use the same cap)
     const void* fn;
     if (oneshot) fn = a.wire_bf16 ? (const void*)fedavg_oneshot_kernel<true> : (const void*)fedavg_oneshot_kernel<false>;
     else fn = a.wire_bf16 ? (const void*)fedavg_twoshot_kernel<true> : (const void*)fedavg_twoshot_kernel<false>;
@@ -742,10 +743,11 @@ int fedavg_aggregate_local(cs_comm** g, int world, float* const* local, float* c
     return launch_agg(g[0]->group_dev, world, world, g[0]->bytes, a, st);
 }
 
-static int launch_inplace(const CommDev* ctxs, int ranks, const InplaceCall& a, cudaStream_t st) {
+static int launch_inplace(const CommDev* ctxs, int ranks, const InplaceCall& a, cudaStream_t st, int max_blocks = 0) {
     CS_REQUIRE(a.n > 0 && a.n % 4 == 0, "aggregate_inplace: n must be a positive multiple of 4");
     CS_REQUIRE(a.channel >= 0 && a.channel < kChannels, "aggregate_inplace: bad channel");
     int nb = pick_blocks(a.n, false);
+    if (max_blocks > 0 && nb > max_blocks) nb = max_blocks;
     const void* fn = (const void*)fedavg_inplace_kernel;
     if (ranks > 1) {
         int per_sm = 1;
@@ -768,7 +770,7 @@ int fedavg_aggregate_inplace(cs_comm* c, size_t param_off, float* prev, long lon
     a.param_off[0] = param_off; a.prev[0] = prev; a.mom[0] = mom;
     for (int r = 0; r < c->world; ++r) a.weights[r] = weights[r];
     a.n = n; a.server_lr = server_lr; a.channel = channel;
-    return launch_inplace(c->dev, 1, a, st);
+    return launch_inplace(c->dev, 1, a, st, c->max_blocks);
 }
 
 int fedavg_aggregate_inplace_local(cs_comm** g, int world, size_t param_off, float* const* prev, long long n,
@@ -875,6 +877,11 @@ int comm_set_timeout_ms(cs_comm* c, long long ms) {
         CS_CUDA_OK(cudaMemcpy(&members[r]->dev->timeout_ns, &v, sizeof(v), cudaMemcpyHostToDevice));
         if (c->emulated) CS_CUDA_OK(cudaMemcpy(&c->group_dev[r].timeout_ns, &v, sizeof(v), cudaMemcpyHostToDevice));
     }
+    return CS_OK;
+}
+int comm_set_max_blocks(cs_comm* c, int n) {
+    CS_REQUIRE(c != nullptr && n >= 0 && n <= kMaxBlocks, "comm_set_max_blocks: bad arguments");
+    c->max_blocks = n;
     return CS_OK;
 }
 int comm_clear_status(cs_comm* c) {

@@ -304,6 +304,10 @@ int cs_comm_status(cs_comm_t* c, int* status_out);
  * (default 4000 ms, or the environment variable CS_COMM_TIMEOUT_MS at creation) */
 int cs_comm_set_timeout_ms(cs_comm_t* c, long long ms);
 int cs_comm_clear_status(cs_comm_t* c);
+/* cap the CTAs of the aggregation / bucket all-reduce launches on this communicator (0 = size by the vector).  A collective
+ * that runs UNDER backward (cs_allreduce_bucket from the gradient hooks) should leave the SMs to backward: its CTAs spin at
+ * the cross-GPU barriers.  The work partition depends on the count, so every rank must set the same value. */
+int cs_comm_set_max_blocks(cs_comm_t* c, int n);
 
 /* K9: device-side barrier across ranks (one tiny kernel; st.release.sys / ld.acquire.sys flags in
  * the peers' signal pads).  `channel` (0..7) selects an independent flag set so collectives on
