@@ -1,5 +1,7 @@
-"""Regenerate profiles/sass/: per-kernel mnemonic histograms + excerpts from `cuobjdump -sass`."""
+"""Regenerate profiles/sass/: per-kernel mnemonic histograms + the FULL `cuobjdump -sass` listing of every hot kernel
+(gzip-compressed, one file per kernel)."""
 import collections
+import gzip
 import os
 import re
 import subprocess
@@ -8,7 +10,8 @@ import sys
 REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(REPO, "lib", "libcrossscale_cuda.so")
 OUT = os.path.join(REPO, "profiles", "sass")
-KERNELS = ["tiny_umma_kernelILi4ELb0ELi2E", "tiny_umma_kernelILi4ELb1ELi2E", "tiny_ecg_f32_kernelILi2E", "conv1d_fwd_kernel",
+KERNELS = ["tiny_round_kernelILi4ELb0E", "tiny_round_kernelILi4ELb1E", "fedavg_bucket_kernel", "fedavg_oneshot_kernelILb1E",
+           "bn_stats_finalize", "bn_bwd_reduce_ws", "mma_probe_kernelILi64ELi16ELb1ELi1E", "tiny_umma_kernelILi4ELb0ELi2E", "tiny_umma_kernelILi4ELb1ELi2E", "tiny_ecg_f32_kernelILi2E", "conv1d_fwd_kernel",
            "conv1d_wgrad_kernel", "conv1d_fwd_sw128_kernel", "conv1d_fwd_pair_kernel", "conv1d_wgrad_sw128_kernel", "bn_apply_coef_kernel",
            "bn_bwd_apply_coef_kernel", "fedavg_oneshot_kernelILb0E", "fedavg_twoshot_kernelILb0E", "fedavg_twoshot_kernelILb1E",
            "fedavg_inplace_kernel", "fedavg_nvls_kernel", "barrier_kernel", "bn_stats_kernel", "bn_bwd_reduce_kernel",
@@ -18,7 +21,8 @@ KEEP = re.compile(r"UTC|LDTM|STTM|UTMA|SYNCS|REDG|ATOMG|MEMBAR|ERRBAR|ELECT|ACQB
 
 HEAD = """# SASS evidence (`cuobjdump -sass lib/libcrossscale_cuda.so`, sm_100a)
 
-Histogram of the tensor-core / TMA / TMEM / NVLink-relevant mnemonics per kernel.
+Histogram of the tensor-core / TMA / TMEM / NVLink-relevant mnemonics per kernel; the complete listing of each kernel is
+next to this file as `<mangled name>.sass.gz` (`zcat` it).
 `UTCHMMA` = tcgen05.mma kind::f16, `LDTM` = tcgen05.ld, `UTCBAR` = tcgen05.commit, `UTCATOMSWS` = tcgen05.alloc/dealloc,
 `UTMALDG.4D` / `UTMALDG.3D` = cp.async.bulk.tensor (TMA load), `UTMASTG.3D` = TMA store, `SYNCS.*` = mbarrier, `REDG.E.ADD.F32x4` = red.global.add.v4.f32,
 `STG/LDG.E.STRONG.SYS` + `MEMBAR.*.SYS` = the st.release.sys / ld.acquire.sys flag protocol of the cross-GPU barrier
@@ -30,7 +34,7 @@ Histogram of the tensor-core / TMA / TMEM / NVLink-relevant mnemonics per kernel
 def main():
     os.makedirs(OUT, exist_ok=True)
     for old in os.listdir(OUT):                            # stale excerpts of kernels that changed signature
-        if old.endswith(".sass.txt"):
+        if old.endswith(".sass.txt") or old.endswith(".sass.gz"):
             os.remove(os.path.join(OUT, old))
     sass = subprocess.run(["cuobjdump", "-sass", LIB], capture_output=True, text=True).stdout
     md = [HEAD]
@@ -42,13 +46,10 @@ def main():
         cnt = collections.Counter(m.group(1) for m in map(MN.match, lines) if m)
         md.append(f"\n## `{name}`\n\ntotal SASS instructions: {sum(cnt.values())}\n\n| mnemonic | count |\n|---|---|")
         md += [f"| {k} | {cnt[k]} |" for k in sorted((k for k in cnt if KEEP.match(k)), key=lambda k: -cnt[k])]
-        pick = [i for i, l in enumerate(lines) if "UTCHMMA" in l or "UTMALDG" in l or "LDGMC" in l or ".SYS" in l]
-        if pick:
-            lo = max(0, pick[0] - 12)
-            ex = [l[:130].rstrip() for l in lines[lo:lo + 70] if re.search(r"/\*[0-9a-f]{4,5}\*/\s+\S", l)]
-            short = re.sub(r"[^A-Za-z0-9]+", "_", name)[:72]
-            with open(os.path.join(OUT, short + ".sass.txt"), "w") as fh:
-                fh.write(f"// excerpt of {name} around its first tensor-core / TMA / system-scope instruction\n" + "\n".join(ex) + "\n")
+        short = re.sub(r"[^A-Za-z0-9]+", "_", name)[:72]
+        with gzip.open(os.path.join(OUT, short + ".sass.gz"), "wt") as fh:
+            fh.write(f"// cuobjdump -sass of {name}\n" + "\n".join(l.rstrip() for l in lines) + "\n")
+        md.append(f"\nfull listing: `{short}.sass.gz`")
     with open(os.path.join(OUT, "README.md"), "w") as fh:
         fh.write("\n".join(md) + "\n")
     print("wrote", OUT)
