@@ -106,8 +106,9 @@ def main():
     elif a.quick:
         grid = [(256, 500, 16, 5), (256, 500, 64, 7), (256, 500, 256, 7), (1024, 500, 128, 3), (64, 500, 256, 31)]
     else:
-        grid = [(B, 500, C, K) for B in (32, 256, 1024, 4096) for C in (16, 64, 256) for K in (3, 7, 31)
-                if B * C * K <= 4096 * 256 * 7]
+        grid = [(B, 500, C, K) for B in (32, 256, 1024, 4096) for C in (16, 64, 256) for K in (3, 7, 31)]   # all 36 cases
+    from crossscale.utils.clocks import ClockSampler
+    sampler = ClockSampler(gpu_index=0).start()
     rows = []
     for case in grid:
         r = bench_case(*case)
@@ -118,7 +119,11 @@ def main():
     if os.path.exists(a.out):
         os.remove(a.out)
     append_results(rows, a.out)
-    print("wrote", a.out)
+    clocks = sampler.stop()
+    import json
+    with open(os.path.splitext(a.out)[0] + "_clocks.json", "w") as fh:
+        json.dump(clocks, fh)
+    print("wrote", a.out, "clocks", clocks)
 
 
 if __name__ == "__main__":

@@ -67,7 +67,41 @@ def load_reference_kernel():
     return None
 
 
-def bench_pair(bs: int, k: int, nthreads: int, rng, ref_lib=None, trials: int = TRIALS):
+def gpu_arm(x: np.ndarray, w: np.ndarray, trials: int):
+    """The same single-channel valid convolution on the GPU (``cs_conv1d_batch_valid``).  Returns (median ms end to end
+    from pinned host memory incl. H2D of x / D2H of y - the host-array contract of the reference's ctypes call -,
+    median ms of the kernel alone, max abs difference to the CPU kernel)."""
+    from ..ops import _lib
+    lib = _lib.cuda_lib()
+    dev = torch.device("cuda", 0)
+    bs, ln = x.shape
+    k = w.shape[0]
+    hx = torch.from_numpy(x).pin_memory()
+    hy = torch.empty((bs, ln - k + 1), dtype=torch.float32).pin_memory()
+    dx, dy = torch.empty_like(hx, device=dev), torch.empty_like(hy, device=dev)
+    dw = torch.from_numpy(w).to(dev)
+    st = _lib.stream_ptr()
+
+    def e2e():
+        dx.copy_(hx, non_blocking=True)
+        _lib.check(lib.cs_conv1d_batch_valid(dx.data_ptr(), dw.data_ptr(), dy.data_ptr(), bs, ln, k, st), "cs_conv1d_batch_valid")
+        hy.copy_(dy, non_blocking=True)
+        torch.cuda.synchronize()
+
+    t_e2e, t_dev = [], []
+    for _ in range(trials):
+        t_e2e.append(time_once(e2e))
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        _lib.check(lib.cs_conv1d_batch_valid(dx.data_ptr(), dw.data_ptr(), dy.data_ptr(), bs, ln, k, st), "cs_conv1d_batch_valid")
+        b.record()
+        torch.cuda.synchronize()
+        t_dev.append(a.elapsed_time(b))
+    err = float(np.abs(hy.numpy() - cpu_conv.conv1d_batch(x, w, 1)).max())
+    return statistics.median(t_e2e), statistics.median(t_dev), err
+
+
+def bench_pair(bs: int, k: int, nthreads: int, rng, ref_lib=None, trials: int = TRIALS, gpu: bool = False):
     x = rng.normal(size=(bs, L)).astype(np.float32)
     w = rng.normal(size=(k,)).astype(np.float32)
     conv = torch.nn.Conv1d(1, 1, k, bias=False)
@@ -98,6 +132,13 @@ def bench_pair(bs: int, k: int, nthreads: int, rng, ref_lib=None, trials: int = 
     if t_ref:
         out.update(_stats("ref", t_ref))
         out["ref_speedup_med"] = out["torch_ms_median"] / out["ref_ms_median"]
+    if gpu:
+        g_e2e, g_dev, err = gpu_arm(x, w, trials)
+        out["gpu_e2e_ms_median"], out["gpu_kernel_ms_median"], out["gpu_max_abs_err"] = g_e2e, g_dev, err
+        out["gpu_e2e_speedup_vs_torch_cpu"] = out["torch_ms_median"] / g_e2e
+        if t_ref:
+            out["gpu_e2e_speedup_vs_reference_c"] = out["ref_ms_median"] / g_e2e
+            out["gpu_kernel_speedup_vs_reference_c"] = out["ref_ms_median"] / g_dev
     return out, raw
 
 
@@ -117,6 +158,7 @@ def main(argv=None):
     ap.add_argument("--batch-sizes", nargs="+", type=int, default=BATCH_SIZES)
     ap.add_argument("--kernel-sizes", nargs="+", type=int, default=KERNEL_SIZES)
     ap.add_argument("--no-ref", action="store_true", help="skip the unmodified reference C kernel arm")
+    ap.add_argument("--gpu", action="store_true", help="add the GPU arm (cs_conv1d_batch_valid on cuda:0)")
     args = ap.parse_args(argv)
     nthreads = os.cpu_count() or 1
     torch.set_num_threads(nthreads)
@@ -129,7 +171,7 @@ def main(argv=None):
     rows, raws = [], []
     for bs in args.batch_sizes:
         for k in args.kernel_sizes:
-            r, raw = bench_pair(bs, k, nthreads, rng, ref_lib, args.trials)
+            r, raw = bench_pair(bs, k, nthreads, rng, ref_lib, args.trials, gpu=args.gpu and torch.cuda.is_available())
             rows.append(r)
             raws.extend(raw)
             extra = f" | reference C kernel {r['ref_speedup_med']:.2f}x" if "ref_speedup_med" in r else ""

@@ -95,6 +95,7 @@ _CUDA_SIGS = {
     "cs_allreduce_bucket_local": (i32, [C.POINTER(vp), i32, C.POINTER(vp), i64, f32, i32, sz, i32, vp]),
     "cs_stage_h2d": (i32, [vp, vp, sz, vp]),
     "cs_stage_d2h": (i32, [vp, vp, sz, vp]),
+    "cs_conv1d_batch_valid": (i32, [vp, vp, vp, i32, i32, i32, vp]),
     "cs_zscore_rows": (i32, [vp, vp, i32, i32, i32, vp]),
 }
 

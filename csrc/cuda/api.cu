@@ -40,6 +40,7 @@ int gather_rows(const float*, const int64_t*, const int64_t*, void*, int64_t*, i
 int cross_entropy(const float*, const int64_t*, int, int, const float*, float*, float*, cudaStream_t);
 int sgd_momentum(float*, float*, const float*, int64_t, float, float, float, int, int32_t*, float*, float, float, int, void*, cudaStream_t);
 int zscore_rows(const float*, void*, int, int, int, cudaStream_t);
+int conv1d_valid_f32(const float*, const float*, float*, int, int, int, cudaStream_t);
 int bn_stats(const void*, float*, int64_t, int, cudaStream_t);
 int bn_stats_finalize(const void*, float*, int32_t*, float*, float*, float*, float*, int64_t, int, float, float, const float*, const float*, float*, cudaStream_t);
 int bn_bwd_reduce_ws(const void*, const void*, const void*, const float*, const float*, float*, int32_t*, float*, float*, float*, float*, const float*, float*, int64_t, int, int, cudaStream_t);
@@ -330,6 +331,9 @@ int cs_stage_h2d(void* dst, const void* src, size_t bytes, cs_stream_t s) {
 int cs_stage_d2h(void* dst, const void* src, size_t bytes, cs_stream_t s) {
     CS_CUDA_OK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, ST(s)));
     return CS_OK;
+}
+int cs_conv1d_batch_valid(const float* x, const float* w, float* y, int batch, int L, int K, cs_stream_t s) {
+    return conv1d_valid_f32(x, w, y, batch, L, K, ST(s));
 }
 int cs_zscore_rows(const float* x, void* y, int B, int L, int out_bf16, cs_stream_t s) {
     return zscore_rows(x, y, B, L, out_bf16, ST(s));

@@ -199,6 +199,39 @@ __global__ void zscore_rows_kernel(const float* __restrict__ x, void* __restrict
     }
 }
 
+// The reference's native kernel on the GPU, same contract: single-channel VALID cross-correlation, fp32,
+// y[b, i] = sum_k x[b, i + k] * w[k], outL = L - K + 1 (ref: Module_2/conv1d_openmp_simd.c:21-61).  One CTA = 1024 outputs
+// of one row: the window (+ K - 1 halo) and the taps are staged in shared memory, each thread produces 4 outputs.
+__global__ void __launch_bounds__(256) conv1d_valid_f32_kernel(const float* __restrict__ x, const float* __restrict__ w,
+                                                               float* __restrict__ y, int L, int K, int outL) {
+    extern __shared__ float cv[];
+    float* ws = cv;                        // [K]
+    float* xs = cv + ((K + 3) & ~3);       // [1024 + K - 1]
+    const int b = blockIdx.y, i0 = blockIdx.x * 1024;
+    const float* xr = x + (size_t)b * L;
+    for (int k = threadIdx.x; k < K; k += 256) ws[k] = w[k];
+    for (int i = threadIdx.x; i < 1024 + K - 1; i += 256) xs[i] = (i0 + i < L) ? __ldg(xr + i0 + i) : 0.0f;
+    __syncthreads();
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+        const int i = threadIdx.x + r * 256;
+        if (i0 + i < outL) {
+            float a = 0.0f;
+            for (int k = 0; k < K; ++k) a = fmaf(xs[i + k], ws[k], a);
+            y[(size_t)b * outL + i0 + i] = a;
+        }
+    }
+}
+
+int conv1d_valid_f32(const float* x, const float* w, float* y, int B, int L, int K, cudaStream_t st) {
+    CS_REQUIRE(B >= 1 && K >= 1 && K <= 1024 && L >= K, "conv1d_valid: bad shape B=%d L=%d K=%d", B, L, K);
+    const int outL = L - K + 1;
+    const size_t smem = (((size_t)K + 3) / 4 * 4 + 1024 + K) * sizeof(float);
+    conv1d_valid_f32_kernel<<<dim3((outL + 1023) / 1024, B), 256, smem, st>>>(x, w, y, L, K, outL);
+    CS_CUDA_OK(cudaGetLastError());
+    return CS_OK;
+}
+
 int zscore_rows(const float* x, void* y, int B, int L, int out_bf16, cudaStream_t st) {
     CS_REQUIRE(B > 0 && L > 0, "zscore: bad shape");
     int blocks = (B + 7) / 8; int cap = num_sms() * 8; if (blocks > cap) blocks = cap;

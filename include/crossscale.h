@@ -395,6 +395,11 @@ int cs_allreduce_bucket_local(cs_comm_t** group, int world, float* const* grads,
  * ------------------------------------------------------------------------------------------- */
 int cs_stage_h2d(void* dst_device, const void* src_pinned_host, size_t bytes, cs_stream_t stream);
 int cs_stage_d2h(void* dst_pinned_host, const void* src_device, size_t bytes, cs_stream_t stream);
+/* The reference's native CPU kernel on the GPU, same contract (device pointers): single-channel VALID cross-correlation,
+ * fp32, y[b,i] = sum_k x[b,i+k]*w[k], y is [batch, L-K+1].  ref: conv1d_batch_omp_simd, Module_2/conv1d_openmp_simd.c:21-61
+ * (the GPU arm of the Part-2 benchmark, Module_2/benchmark_part_2.py:12-19). */
+int cs_conv1d_batch_valid(const float* x, const float* w, float* y, int batch, int L, int K, cs_stream_t stream);
+
 /* y[b,:] = (x[b,:]-mean_b)/(std_b+1e-8) per window; out_bf16 selects the output type */
 int cs_zscore_rows(const float* x, void* y, int B, int L, int out_bf16, cs_stream_t stream);
 

@@ -292,3 +292,17 @@ def test_fedavg_runner_with_resnet_small(synth_shards=None):
     assert not r.fused and r.kernel_generic and rows[-1]["avg_loss"] < rows[0]["avg_loss"] + 0.05
     assert rows[0]["comm_ms"] > 0 and r.agg.backend == "kernel"
     r.close()
+
+
+@pytest.mark.parametrize("B,L,K", [(64, 500, 3), (512, 500, 7), (5, 1300, 32), (3, 40, 40)])
+def test_conv1d_batch_valid_matches_reference_semantics(B, L, K):
+    """GPU arm of the reference's native kernel (single-channel valid cross-correlation, conv1d_openmp_simd.c:21-61)
+    against F.conv1d in fp32."""
+    from crossscale.ops import _lib
+    dev = torch.device("cuda", 0)
+    torch.manual_seed(0)
+    x, w = torch.randn(B, L, device=dev), torch.randn(K, device=dev)
+    y = torch.empty(B, L - K + 1, device=dev)
+    _lib.check(_lib.cuda_lib().cs_conv1d_batch_valid(x.data_ptr(), w.data_ptr(), y.data_ptr(), B, L, K, _lib.stream_ptr()))
+    ref = torch.nn.functional.conv1d(x.unsqueeze(1), w.view(1, 1, K)).squeeze(1)
+    torch.testing.assert_close(y, ref, rtol=1e-5, atol=1e-5)
