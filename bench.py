@@ -267,6 +267,8 @@ def run_ours(args):
                 "windows_ms_per_step": [round(t / K, 5) for t in ms2],
                 "loss_scale": r2.trainer.state.loss_scale(), "skipped_steps": r2.trainer.state.skipped_steps(),
                 "one_launch_per_round": bool(r2.trainer.use_round)}
+            if amp == "none":                                # G0: fp32 storage / accumulation / conv1 / head / SGD; conv2 operands as TF32
+                arms["fp32"]["conv2_operands"] = "tf32 (tcgen05.mma kind::tf32)" if r2.trainer.use_round else "fp32 FFMA"
             r2.close()
     clocks = sampler.stop()
 

@@ -108,7 +108,7 @@ def measure_a5(device: torch.device, batch: int, iters: int, num_classes: int, d
     stager, sampler = H2DStager(rows, store.l, dt, device), BlockSampler(store.n, rows, seed=0)
     model = TinyECG(num_classes).to(device)
     st = tk.TinyTrainState(model.flatten_parameters().flat, num_classes, lr=1e-2, momentum=0.0, amp=tk.AMP_BY_NAME[amp])
-    use_round = st.round_supported() and tk.round_kernel_available()
+    use_round = st.round_supported(store.l) and tk.round_kernel_available()
     blocks = max(2, (iters + steps_per_block - 1) // steps_per_block)
     t_data = 0.0
 

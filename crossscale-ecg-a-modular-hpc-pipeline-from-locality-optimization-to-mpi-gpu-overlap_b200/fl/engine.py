@@ -288,8 +288,10 @@ class FusedTinyTrainer:
 
     G1 (bf16 / fp16): the persistent round kernel - ``local_steps`` steps (and, when the caller passes
     ``fused_agg``, the FedAvg aggregation) are ONE cooperative launch; batches come from the kernel's own
-    per-epoch permutation, so no ``randperm`` / index copy is on the stream.  G0 (fp32) and ``use_round=False``:
-    one launch per step, a round's launches captured once in a CUDA graph."""
+    per-epoch permutation, so no ``randperm`` / index copy is on the stream.  G0 (fp32) takes the same path with
+    fp32 operands fed to the tensor core as TF32 (what cuDNN does for the reference's fp32 convolutions by default);
+    ``CROSSSCALE_G0_TF32=0`` or ``use_round=False``: one launch per step (G0: the fp32 FFMA kernel), a round's launches
+    captured once in a CUDA graph."""
 
     def __init__(self, model: TinyECG, x_gpu: torch.Tensor, y_gpu: torch.Tensor, batch: int,
                  local_steps: int, lr=1e-2, momentum=0.9, amp: str = "none", use_graph: bool = True,
@@ -309,7 +311,7 @@ class FusedTinyTrainer:
             raise ValueError(f"dataset has {x_gpu.shape[0]} windows < batch {batch}")
         if use_round is None:
             use_round = os.environ.get("CROSSSCALE_TINY_ROUND", "1") != "0"
-        self.use_round = bool(use_round) and self.state.round_supported() and tk.round_kernel_available()
+        self.use_round = bool(use_round) and self.state.round_supported(int(x_gpu.shape[1])) and tk.round_kernel_available()
         self.seed = int(generator.initial_seed() if generator is not None else torch.initial_seed()) & ((1 << 63) - 1)
         self.stream_idx = None if self.use_round else IndexStream(x_gpu.shape[0], batch, x_gpu.device, generator)
         self.idx = None if self.use_round else torch.zeros(local_steps * batch, dtype=torch.int64, device=x_gpu.device)

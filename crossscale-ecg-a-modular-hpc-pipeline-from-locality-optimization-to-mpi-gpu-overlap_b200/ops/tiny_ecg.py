@@ -174,8 +174,13 @@ class TinyTrainState:
         self.launches = 0
         self.gacc_round: Optional[torch.Tensor] = None
 
-    def round_supported(self) -> bool:
-        return self.amp != AMP_FP32
+    def round_supported(self, window: Optional[int] = None) -> bool:
+        """bf16 / fp16: always.  fp32 runs the round on the tensor core as TF32 (tiny_ecg_round_tf32.cu,
+        windows up to 512 samples); CROSSSCALE_G0_TF32=0 keeps G0 on the fp32 FFMA step kernel."""
+        if self.amp != AMP_FP32:
+            return True
+        import os
+        return os.environ.get("CROSSSCALE_G0_TF32", "1") != "0" and (window is None or window <= 512)
 
     def round(self, x: torch.Tensor, y: torch.Tensor, steps: int, batch: int, idx: Optional[torch.Tensor] = None,
               sample_mode: int = SAMPLE_IDX, seed: int = 0, comm=None, prev: Optional[torch.Tensor] = None,

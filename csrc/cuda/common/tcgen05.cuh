@@ -118,7 +118,16 @@ __device__ __forceinline__ uint64_t smem_desc_sw128_mn(uint32_t saddr, uint32_t 
     return d;
 }
 
-enum : uint32_t { FMT_F16 = 0, FMT_BF16 = 1 };
+// MN-major operand of a 32-bit type (kind::tf32): layout type 1 = 128-byte swizzle with a 32-byte base, the only form the
+// tensor core reads for it (measured: the no-swizzle MN-major descriptor yields zeros for tf32).  Element (mn, k) sits at
+//   L = start + (mn/32)*LBO + (k/4)*SBO + (k%4)*128 + (mn%32)*4,   physical address = L ^ ((L >> 2) & 0x60)
+// i.e. every K row is 128 B = 32 values along MN and its four 32-byte chunks are permuted by address bits 7..8.  The swizzle
+// acts on the absolute shared address, so a start address shifted by whole rows needs no base offset (arrays 512-aligned).
+__device__ __forceinline__ uint64_t smem_desc_mn32(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+    return smem_desc(saddr, lbo_bytes, sbo_bytes) | ((uint64_t)1 << 61);
+}
+
+enum : uint32_t { FMT_F16 = 0, FMT_BF16 = 1, FMT_TF32 = 2 };
 enum : uint32_t { MAJOR_K = 0, MAJOR_MN = 1 };
 // kind::f16 instruction descriptor: D=f32, A/B format, majors, N>>3 at bit 17, M>>4 at bit 24
 __host__ __device__ constexpr uint32_t idesc_f16(uint32_t fmt, uint32_t M, uint32_t N, uint32_t a_major, uint32_t b_major) {
@@ -131,6 +140,22 @@ __device__ __forceinline__ void mma_f16(uint32_t d_tmem, uint64_t adesc, uint64_
         "{\n\t.reg .pred p;\n\t"
         "setp.ne.b32 p, %4, 0;\n\t"
         "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+// kind::tf32: 32-bit operands (fp32 bit patterns, the tensor core reads the top 19 bits), K = 8 per instruction, fp32 accumulate;
+// fp32 -> nearest tf32 (10 mantissa bits) kept in an fp32 container.  kind::tf32 itself just DROPS the low 13 bits of
+// whatever it is fed, a bias towards zero that adds up coherently over a long reduction; operands are rounded when written.
+__device__ __forceinline__ float to_tf32(float x) {
+    uint32_t r;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+    return __uint_as_float(r);
+}
+// same descriptor formats as kind::f16 with a/b format = FMT_TF32
+__device__ __forceinline__ void mma_tf32(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
         ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
 }
 // all previously issued MMAs of this thread arrive on `bar` when they complete

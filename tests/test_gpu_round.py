@@ -251,3 +251,118 @@ def test_round_fused_aggregation_emulated_clients(world, wire):
             assert _rel(fused[r].mom[:n], solo[r].mom[:n]) < 5e-4             # momentum stays local
             solo[r].mom.copy_(fused[r].mom)
     group.close()
+
+
+# ---- G0: fp32 operands on the tensor core as TF32 (tiny_ecg_round_tf32.cu) -----------------------------------------------------
+@pytest.mark.parametrize("Cn,B,L,steps", [(2, 256, 500, 8), (5, 37, 360, 7), (2, 400, 500, 3), (3, 9, 129, 4), (2, 64, 512, 1), (8, 3, 64, 2)])
+def test_round_tf32_matches_fp32_step_kernel(Cn, B, L, steps):
+    """amp = fp32 through the persistent round (tcgen05 kind::tf32, fp32 accumulation, conv1/head/SGD in fp32 FFMA) against
+    `steps` launches of the fp32 FFMA step kernel on the same batches.  TF32 keeps 10 mantissa bits of each conv2 operand, so
+    the two agree to ~1e-3 of the update, far tighter than bf16 (8 bits)."""
+    _need_sm100()
+    from crossscale.ops import tiny_ecg as tk
+    m = _model(Cn, seed=5)
+    x, y = _data(3000, L, Cn)
+    idx = torch.randint(0, x.shape[0], (steps * B,), device=_dev())
+    a, b = _state(m, Cn, "none"), _state(m, Cn, "none")
+    start = a.params.clone()
+    for s in range(steps):
+        a.step(x, y, idx[s * B:(s + 1) * B], batch=B)
+    assert b.round_supported(L)
+    b.round(x, y, steps, B, idx=idx, sample_mode=tk.SAMPLE_IDX)
+    torch.cuda.synchronize()
+    b.check_errors()
+    n = 1424 + 17 * Cn
+    upd = _rel(b.params[:n] - start[:n], a.params[:n] - start[:n])
+    assert upd < 4e-3, upd                                   # error relative to the UPDATE, not to the parameters
+    assert _rel(b.params[:n], a.params[:n]) < 2e-4
+    assert abs(b.loss_sum() - a.loss_sum()) < 1e-3 * max(1.0, abs(a.loss_sum()))
+    assert b.steps_done() == steps
+    assert int(b.ctrl[tk.CTRL_TICKET]) == 0 and float(b.gacc_round.abs().max()) == 0.0
+    b.round(x, y, steps, B, idx=idx, sample_mode=tk.SAMPLE_IDX)              # a second round on the same state
+    for s in range(steps):
+        a.step(x, y, idx[s * B:(s + 1) * B], batch=B)
+    torch.cuda.synchronize()
+    b.check_errors()
+    assert _rel(b.params[:n], a.params[:n]) < 4e-4
+
+
+def test_round_tf32_tracks_fp32_torch_sgd_and_beats_bf16():
+    """fp32 oracle (nn.Module + F.cross_entropy + torch.optim.SGD, TF32 off): the tf32 round must sit closer to it than the
+    bf16 round on the same batches."""
+    _need_sm100()
+    from crossscale.models import TinyECG
+    Cn, B, L, steps = 5, 128, 360, 6
+    m = _model(Cn, seed=3)
+    ref = TinyECG(Cn).to(_dev())
+    ref.load_state_dict(m.state_dict())
+    opt = torch.optim.SGD(ref.parameters(), lr=1e-2, momentum=0.9)
+    x, y = _data(2000, L, Cn, seed=9)
+    idx = torch.randint(0, x.shape[0], (steps * B,), device=_dev())
+    st32, st16 = _state(m, Cn, "none"), _state(m, Cn, "bf16")
+    st32.round(x, y, steps, B, idx=idx)
+    st16.round(x, y, steps, B, idx=idx)
+    old = torch.backends.cudnn.allow_tf32
+    torch.backends.cudnn.allow_tf32 = False
+    try:
+        losses = []
+        for s in range(steps):
+            sel = idx[s * B:(s + 1) * B]
+            opt.zero_grad(set_to_none=True)
+            loss = F.cross_entropy(ref.forward_reference(x[sel].unsqueeze(1)), y[sel])
+            loss.backward()
+            opt.step()
+            losses.append(float(loss))
+    finally:
+        torch.backends.cudnn.allow_tf32 = old
+    torch.cuda.synchronize()
+    st32.check_errors()
+    want = torch.cat([p.detach().reshape(-1) for p in ref.parameters()])
+    e32, e16 = _rel(st32.params[:want.numel()], want), _rel(st16.params[:want.numel()], want)
+    assert e32 < 5e-4, e32
+    assert e32 < e16, (e32, e16)
+    assert st32.loss_sum() == pytest.approx(sum(losses), rel=2e-3)
+
+
+def test_round_tf32_permutation_sampler_and_fused_aggregation():
+    """the tf32 kernel shares the sampler and the FedAvg tail with the bf16 one: 3 emulated clients, in-kernel permutation."""
+    _need_sm100()
+    from crossscale.ops import _lib, tiny_ecg as tk
+    from crossscale.parallel.symm import LocalGroup, ptr_array
+    Cn, B, L, steps, world, rows = 2, 48, 360, 3, 3, 500
+    lib = _lib.cuda_lib()
+    m = _model(Cn, seed=12)
+    n = 1424 + 17 * Cn
+    wts = [0.5, 0.3, 0.2]
+    xs, ys, solo, fused, prevs = [], [], [], [], []
+    for r in range(world):
+        x, y = _data(rows, L, Cn, seed=20 + r)
+        xs.append(x); ys.append(y)
+        solo.append(_state(m, Cn, "none")); fused.append(_state(m, Cn, "none"))
+        prevs.append(fused[r].params.clone())
+        fused[r].gacc_round = torch.zeros(int(lib.cs_tiny_ecg_round_scratch_floats(Cn)), device=_dev())
+    start = prevs[0].clone()
+    for r in range(world):
+        idx = torch.tensor(tk.perm_batches(0, steps * B, rows, B, 77 + r), dtype=torch.int64, device=_dev())
+        for s in range(steps):
+            solo[r].step(xs[r], ys[r], idx[s * B:(s + 1) * B], batch=B)
+    group = LocalGroup(world, int(lib.cs_fedavg_arena_bytes(n, 0, world)))
+    w = (C.c_float * world)(*wts)
+    nrows = (C.c_int64 * world)(*[rows] * world)
+    seeds = (C.c_uint64 * world)(*[77 + r for r in range(world)])
+    _lib.check(lib.cs_tiny_ecg_train_round_local(
+        group.handles, world, ptr_array(xs), ptr_array(ys), None, 0, nrows, B, L, Cn, steps, tk.SAMPLE_PERM,
+        seeds, ptr_array([s.params for s in fused]), ptr_array([s.mom for s in fused]),
+        ptr_array([s.gacc_round for s in fused]), ptr_array([s.ctrl for s in fused]),
+        ptr_array([s.fstate for s in fused]), 1e-2, 0.9, 0.0, tk.AMP_FP32, 0, 2.0, 0.5, 2000, ptr_array(prevs), w,
+        0, 1.0, 0, 0, 0, _lib.stream_ptr()), "cs_tiny_ecg_train_round_local")
+    torch.cuda.synchronize()
+    assert group.status() == 0
+    for st in fused:
+        st.check_errors()
+    want = start[:n].double() + sum(wts[r] * (solo[r].params[:n].double() - start[:n].double()) for r in range(world))
+    for r in range(world):
+        assert _rel(fused[r].params[:n], want) < 2e-4, (r, _rel(fused[r].params[:n], want))
+        assert torch.equal(fused[r].params[:n], fused[0].params[:n])
+        assert fused[r].samples_drawn() == steps * B
+    group.close()
