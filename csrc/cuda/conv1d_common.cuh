@@ -51,4 +51,37 @@ int conv1d_fwd_sw128(const void* x, const void* w, const float* bias, void* y, i
 int conv1d_wgrad_sw128(const void* x, const void* dy, float* dw, int B, int L, int Cin, int Cout, int K, int pad, int Lout,
                        cudaStream_t st);
 
+// conv1d_narrow.cu - second generation for narrow layers (channels < 64): persistent, pipelined kernels on the 16-byte
+// plane layout.  Same return convention as the sw128 entry points.
+int conv1d_fwd_narrow(const void* x, const void* w, const float* bias, void* y, int B, int L, int Cin, int Cout, int K, int pad,
+                      int relu, int Lout, cudaStream_t st);
+int conv1d_wgrad_narrow(const void* x, const void* dy, float* dw, int B, int L, int Cin, int Cout, int K, int pad, int Lout,
+                        cudaStream_t st);
+// the same layers as 64-channel layers on packed positions (f positions per 128-byte row) through the sw128 kernels
+int conv1d_fwd_packed(const void* x, const void* w, const float* bias, void* y, int B, int L, int Cin, int Cout, int K, int pad,
+                      int relu, int Lout, cudaStream_t st);
+int conv1d_wgrad_packed(const void* x, const void* dy, float* dw, int B, int L, int Cin, int Cout, int K, int pad, int Lout,
+                        cudaStream_t st);
+
+// planes view of a channels-last bf16 tensor [outer, rows, C]: dims (c8 = 8, row, plane = C/8, outer)
+inline int make_plane_map(CUtensorMap* m, const void* base, int outer, int rows, int C, int box_rows, int box_planes) {
+    EncodeTiledFn fn = encode_fn();
+    CS_REQUIRE(fn != nullptr, "cuTensorMapEncodeTiled not available from this driver");
+    cuuint64_t dims[4] = {8, (cuuint64_t)rows, (cuuint64_t)(C / 8), (cuuint64_t)outer};
+    cuuint64_t strides[3] = {(cuuint64_t)C * 2, 16, (cuuint64_t)rows * C * 2};
+    cuuint32_t box[4] = {8, (cuuint32_t)box_rows, (cuuint32_t)box_planes, 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    CS_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed (%d) rows=%d C=%d box=%dx%d", (int)r, rows, C, box_rows, box_planes);
+    return CS_OK;
+}
+
+__device__ __forceinline__ void tma_load_4d(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1, int c2, int c3) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+        ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
+}
+
 }  // namespace cs

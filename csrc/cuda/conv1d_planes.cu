@@ -22,26 +22,7 @@ namespace cs {
 // ------------------------------------------------------------------------------------------------
 // tensor maps (driver entry point fetched through the runtime: no -lcuda needed)
 // ------------------------------------------------------------------------------------------------
-// planes view of a channels-last bf16 tensor [outer, rows, C]: dims (c8 = 8, row, plane = C/8, outer)
-static int make_plane_map(CUtensorMap* m, const void* base, int outer, int rows, int C, int box_rows, int box_planes) {
-    EncodeTiledFn fn = encode_fn();
-    CS_REQUIRE(fn != nullptr, "cuTensorMapEncodeTiled not available from this driver");
-    cuuint64_t dims[4] = {8, (cuuint64_t)rows, (cuuint64_t)(C / 8), (cuuint64_t)outer};
-    cuuint64_t strides[3] = {(cuuint64_t)C * 2, 16, (cuuint64_t)rows * C * 2};
-    cuuint32_t box[4] = {8, (cuuint32_t)box_rows, (cuuint32_t)box_planes, 1};
-    cuuint32_t estr[4] = {1, 1, 1, 1};
-    CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, box, estr,
-                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
-                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    CS_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed (%d) rows=%d C=%d box=%dx%d", (int)r, rows, C, box_rows, box_planes);
-    return CS_OK;
-}
-
-__device__ __forceinline__ void tma_load_4d(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1, int c2, int c3) {
-    asm volatile(
-        "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
-        ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
-}
+// (make_plane_map / tma_load_4d: conv1d_common.cuh, shared with conv1d_narrow.cu)
 
 // ------------------------------------------------------------------------------------------------
 // K1 forward (dgrad reuses it with flipped / transposed weights)
@@ -210,6 +191,10 @@ int conv1d_fwd(const void* x, const void* w, const float* bias, void* y, int B, 
     {
         const int rc128 = conv1d_fwd_sw128(x, w, bias, y, B, L, Cin, Cout, K, pad, relu, s.Lout, st);
         if (rc128 >= 0) return rc128;
+        const int rcp = conv1d_fwd_packed(x, w, bias, y, B, L, Cin, Cout, K, pad, relu, s.Lout, st);
+        if (rcp >= 0) return rcp;
+        const int rcn = conv1d_fwd_narrow(x, w, bias, y, B, L, Cin, Cout, K, pad, relu, s.Lout, st);
+        if (rcn >= 0) return rcn;
     }
     s.CK = pick_ck(Cin); s.NT = pick_nt(Cout); s.R = 128 + K - 1;
     CUtensorMap mx, mw;
@@ -435,8 +420,14 @@ int conv1d_wgrad(const void* x, const void* dy, float* dw, float* dbias, int B, 
         s.total_tiles = (B + 128 / s.slot - 1) / (128 / s.slot);
         if (splits > s.total_tiles) splits = s.total_tiles;
     }
-    const int rc128 = conv1d_wgrad_sw128(x, dy, dw, B, L, Cin, Cout, K, pad, Lout, st);
+    int rc128 = conv1d_wgrad_sw128(x, dy, dw, B, L, Cin, Cout, K, pad, Lout, st);
     if (rc128 > 0) return rc128;
+    if (rc128 < 0) {                                        // narrow layers: persistent tap-group kernel (conv1d_narrow.cu)
+        int rcn = env_int("CS_CONV_PACK_WGRAD", 0) ? conv1d_wgrad_packed(x, dy, dw, B, L, Cin, Cout, K, pad, Lout, st) : -1;
+        if (rcn < 0) rcn = conv1d_wgrad_narrow(x, dy, dw, B, L, Cin, Cout, K, pad, Lout, st);
+        if (rcn > 0) return rcn;
+        if (rcn == 0) rc128 = 0;
+    }
     for (int k0 = 0; rc128 < 0 && k0 < K; k0 += kWgTapsPerPass) {
         s.k0 = k0; s.ktaps = K - k0 < kWgTapsPerPass ? K - k0 : kWgTapsPerPass;
         s.R = s.slot ? ((128 + s.ktaps - 1 + 7) & ~7) : 128 + s.ktaps - 1;

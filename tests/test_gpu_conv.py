@@ -22,11 +22,28 @@ CASES = [(4, 500, 16, 16, 5, 2), (2, 360, 64, 128, 7, 3), (3, 130, 256, 256, 3, 
          (2, 500, 64, 64, 31, 15), (2, 200, 128, 96, 9, 4), (1, 513, 64, 256, 5, 2),
          # short windows: several samples packed into one 128-row tile (slot 64 / 32 / 16)
          (6, 45, 64, 128, 7, 3), (3, 20, 32, 32, 5, 2), (19, 10, 16, 16, 3, 1), (5, 58, 256, 256, 7, 3), (64, 45, 768, 768, 7, 3),
-         (9, 24, 64, 64, 5, 2), (7, 30, 128, 256, 3, 1)]
+         (9, 24, 64, 64, 5, 2), (7, 30, 128, 256, 3, 1),
+         # narrow layers, persistent second-generation kernels (conv1d_narrow.cu): more work items than SMs (ring wrap-around),
+         # two item groups per sample with a ragged last one, 48/32-channel operands, tap groups of 16
+         (300, 500, 16, 16, 3, 1), (40, 1100, 32, 16, 7, 3), (7, 700, 48, 32, 16, 8), (3, 333, 16, 48, 31, 15), (600, 130, 16, 32, 5, 2)]
 
 
 @pytest.mark.parametrize("B,L,Cin,Cout,K,pad", CASES)
 def test_conv1d_fwd_dgrad_wgrad(B, L, Cin, Cout, K, pad):
+    _check_conv(B, L, Cin, Cout, K, pad)
+
+
+@pytest.mark.parametrize("B,L,Cin,Cout,K,pad", [(6, 500, 16, 16, 3, 1), (5, 360, 16, 32, 31, 15), (3, 512, 32, 16, 7, 3), (4, 128, 32, 64, 5, 0),
+                                                (2, 1000, 16, 48, 9, 4), (3, 400, 16, 16, 4, 3)])
+def test_conv1d_channel_packed_rows(monkeypatch, B, L, Cin, Cout, K, pad):
+    """narrow layers as 64-channel layers on packed positions (conv1d_narrow.cu: 4 or 2 positions per 128-byte row, packed taps
+    with zero blocks) forced on small shapes, forward + data gradient + the packed weight gradient folded back"""
+    monkeypatch.setenv("CS_CONV_PACK_MIN", "0")
+    monkeypatch.setenv("CS_CONV_PACK_WGRAD", "1")
+    _check_conv(B, L, Cin, Cout, K, pad)
+
+
+def _check_conv(B, L, Cin, Cout, K, pad):
     from crossscale.ops.conv1d import Conv1dB200
     torch.manual_seed(B * 100 + K)
     m = Conv1dB200(Cin, Cout, K, padding=pad, bias=True).to(DEV)
