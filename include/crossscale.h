@@ -31,7 +31,7 @@ extern "C" {
 typedef void* cs_stream_t; /* cudaStream_t */
 
 /* precision modes of the fused TinyECG kernels */
-#define CS_AMP_FP32 0 /* G0: fp32 FFMA path                                   */
+#define CS_AMP_FP32 0 /* G0: fp32 (step kernel: FFMA; round kernel: tf32 MMAs)   */
 #define CS_AMP_BF16 1 /* G1: bf16 operands, fp32 accumulate (tcgen05)         */
 #define CS_AMP_FP16 2 /* G1 reference-faithful: fp16 operands + loss scaling  */
 
@@ -114,7 +114,8 @@ int cs_tiny_ecg_train_step_noalloc(const void* x, const int64_t* y, const int64_
 /* K6b persistent: ONE cooperative launch = `steps` local training steps + (optionally) the FedAvg aggregation.
  * ref: the whole round loop body, TRUE_FL_M3/part3_fedavg_overlap_mpi_gpu.py:186-231 (Bcast, 50 x train_step_G1,
  * Allreduce-mean) - here 50 steps x ~40 launches, 50 synchronisations and 36 host-staged collectives become one kernel.
- * tcgen05 path only (amp = CS_AMP_BF16 / CS_AMP_FP16; CS_ERR_INVALID otherwise).  Per step: fused forward/backward
+ * tcgen05 path: amp = CS_AMP_BF16 / CS_AMP_FP16 (16-bit operands), or CS_AMP_FP32 = fp32 storage with the conv2 operands fed to
+ * the tensor core as TF32 (kind::tf32, windows up to 512 samples; what cuDNN does for train_step_G0's fp32 convolutions).  Per step: fused forward/backward
  * per sample, gradients summed through a rotating global scratch, one grid-wide barrier, then every CTA applies
  * SGD-momentum (and the GradScaler rules) to its own shared-memory copy of the model.
  *   sample_mode 0: sample b of step s reads row idx[s*B + b]            (idx int64 [steps*B])
