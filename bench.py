@@ -62,8 +62,27 @@ def make_shards(root: str, rank: int, n: int) -> str:
     return d
 
 
+_REAL_STDOUT = None
+
+
+def quiet_stdout():
+    """Libraries print banners to fd 1 (NCCL: "NCCL version ..." at communicator creation).  The contract is ONE JSON line on
+    stdout, so fd 1 points at stderr until emit() writes that line to the saved descriptor."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
 def emit(obj):
-    print(json.dumps(obj), flush=True)
+    line = json.dumps(obj) + "\n"
+    sys.stdout.flush()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(line)
+        sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, line.encode())
 
 
 # ------------------------------------------------------------------------------------------------
@@ -258,11 +277,16 @@ def run_ours(args):
         for amp in ("fp16", "none", "bf16"):
             if amp == args.amp:
                 continue
-            r2, cfg2 = make_runner(amp)
-            preheat(r2, 48)
-            ms2 = timed_windows(r2.run_round_async, 3)
-            r2.check_health()
-            arms[{"fp16": "fp16_scaler", "none": "fp32", "bf16": "bf16"}[amp]] = {
+            name = {"fp16": "fp16_scaler", "none": "fp32", "bf16": "bf16"}[amp]
+            try:                                             # the headline must survive a failure of a side measurement
+                r2, cfg2 = make_runner(amp)
+                preheat(r2, 48)
+                ms2 = timed_windows(r2.run_round_async, 3)
+                r2.check_health()
+            except Exception as e:
+                arms[name] = {"error": f"{type(e).__name__}: {e}"[:300]}
+                continue
+            arms[name] = {
                 "fl_config": cfg2, "value": samples / (_median(ms2) / 1e3), "ms_per_step": _median(ms2) / K,
                 "windows_ms_per_step": [round(t / K, 5) for t in ms2],
                 "loss_scale": r2.trainer.state.loss_scale(), "skipped_steps": r2.trainer.state.skipped_steps(),
@@ -419,6 +443,7 @@ def run_reference(args):
 
 def main():
     args = parse()
+    quiet_stdout()
     if args.impl == "reference":
         run_reference(args)
     else:
