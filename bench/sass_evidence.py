@@ -11,7 +11,7 @@ REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(REPO, "lib", "libcrossscale_cuda.so")
 OUT = os.path.join(REPO, "profiles", "sass")
 KERNELS = ["tiny_round_tf32_kernel", "conv1d_fwd_narrow_kernel", "conv1d_wgrad_narrow_kernel", "pack_weight_kernel", "unpack_wgrad_kernel",
-           "mma_layout_probe_kernel", "tiny_round_kernelILi4ELb0E", "tiny_round_kernelILi4ELb1E", "fedavg_bucket_kernel", "fedavg_oneshot_kernelILb1E",
+           "mma_layout_probe_kernel", "tma_stream_probe_kernel", "tiny_round_kernelILi4ELb0E", "tiny_round_kernelILi4ELb1E", "fedavg_bucket_kernel", "fedavg_oneshot_kernelILb1E",
            "bn_stats_finalize", "bn_bwd_reduce_ws", "mma_probe_kernelILi64ELi16ELb1ELi1E", "tiny_umma_kernelILi4ELb0ELi2E", "tiny_umma_kernelILi4ELb1ELi2E", "tiny_ecg_f32_kernelILi2E", "conv1d_fwd_kernel",
            "conv1d_wgrad_kernel", "conv1d_fwd_sw128_kernel", "conv1d_fwd_pair_kernel", "conv1d_wgrad_sw128_kernel", "bn_apply_coef_kernel",
            "bn_bwd_apply_coef_kernel", "fedavg_oneshot_kernelILb0E", "fedavg_twoshot_kernelILb0E", "fedavg_twoshot_kernelILb1E",

@@ -48,23 +48,39 @@ __device__ __forceinline__ uint64_t smem_desc_krow(uint32_t saddr, uint32_t sbo_
     return d;
 }
 
+extern long long* g_tiny_prof;   // cs_debug_set_tiny_profile (tiny_ecg_umma.cu)
+
 struct NarrowFwd {
+    long long* prof;   // debug timeline of CTA 0 (null in production)
     int B, L, Lout, Cin, Cout, K, pad, relu;
     int R;             // rows of one activation tile = 128 + K - 1
-    int MT;            // 128-position tiles per work item (<= 4)
-    int groups;        // work items per sample
-    int items;         // B * groups
+    int MT;            // 128-position tiles per work item (<= 4); tiles are numbered b * tiles + t, an item is MT consecutive
+                       // ones (so short packed samples share an item and both MMA warps have work)
+    int units;         // B * tiles
+    int items;         // ceil(units / MT)
     int tiles;         // 128-position tiles per sample
     int NS;            // ring depth
     int a_tile_stride; // bytes of one tile in the ring (1024-aligned: the swizzles act on address bits 7..9)
     int w_tap_bytes;   // Cout * Cin * 2, 1024-aligned
     int w_bytes;       // K taps
+    int stage_bytes;
 };
 
+// tile 0 of work item `item` as a global tile number b * tiles + t, and the number of tiles in the item
+__device__ __forceinline__ void narrow_item(const NarrowFwd& s, int item, int& first, int& mt) {
+    first = item * s.MT;
+    mt = s.units - first < s.MT ? s.units - first : s.MT;
+}
+
 // Operand rows are whole positions: [row = position][Cin x bf16 = 32 / 64 / 128 B], written by TMA with the swizzle of that
-// width (ONE TMA row per position; the plane layout needs Cin / 8 rows of 16 bytes per position, and the TMA unit is
-// row-rate bound: ~3 cycles per 16-byte row measured, i.e. 1.5 TB/s over the whole GPU).  A tap is a start-address shift of
-// one row; the swizzle is a function of the absolute address, so shifted descriptors stay consistent.
+// width: ONE TMA row per position (the plane layout needs Cin / 8 rows of 16 bytes).  What one SM's TMA unit delivers from
+// cold DRAM grows with the bytes per load and does not grow with the ring depth (bench/tma_stream_probe.py, 128-row boxes:
+// 0.93 / 1.82 / 3.35 / 4.5 TB/s over the GPU for 16 / 32 / 64 / 128-byte rows; 1-D bulk copies of 4 / 16 KB: 1.9 / 4.5 TB/s),
+// and C = 16 at K = 3 (37 us for 65.5 MB in = 1.8 TB/s) sits on the 32-byte-row figure; loading the same rows as 256-row
+// boxes was tried and changed nothing.  The channel-packed path below gets 128-byte rows.  A tap is a start-address shift of one
+// row; the swizzle is a function of the absolute address, so shifted descriptors stay consistent.  One MMA's accumulate is
+// ~130 cycles behind its issue when the next MMA targets the same accumulator (timeline of CTA 0, debug hook `prof`), so
+// each issuing warp interleaves its two tiles.
 __global__ void __launch_bounds__(kNarrowThreads, 1)
 conv1d_fwd_narrow_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_w,
                          const float* __restrict__ bias, __nv_bfloat16* __restrict__ y, NarrowFwd s) {
@@ -80,7 +96,7 @@ conv1d_fwd_narrow_kernel(const __grid_constant__ CUtensorMap map_x, const __grid
     float* bias_s = reinterpret_cast<float*>(smem + 256);      // [64]
     uint8_t* w_smem = smem + 1024;
     uint8_t* a_ring = w_smem + s.w_bytes;
-    const int stage_bytes = s.a_tile_stride * s.MT;
+    const int stage_bytes = s.stage_bytes;
     const int buf_cols = s.MT * s.Cout;
     uint32_t tmem_cols = 32;
     while ((int)tmem_cols < 2 * buf_cols) tmem_cols <<= 1;
@@ -107,14 +123,16 @@ conv1d_fwd_narrow_kernel(const __grid_constant__ CUtensorMap map_x, const __grid
             mbar_arrive_expect_tx(w_full, s.K * s.Cout * row_bytes);
             for (int k = 0; k < s.K; ++k) tma_load_3d(w_smem + k * s.w_tap_bytes, &map_w, w_full, 0, 0, k);
             for (int it = 0; it < my_items; ++it) {
-                const int item = blockIdx.x + it * gridDim.x;
-                const int b = item / s.groups, t0 = (item % s.groups) * s.MT;
-                const int mt = s.tiles - t0 < s.MT ? s.tiles - t0 : s.MT;
+                int u0, mt;
+                narrow_item(s, blockIdx.x + it * gridDim.x, u0, mt);
                 const int sa = it % s.NS;
                 if (it >= s.NS) mbar_wait(empty + sa, ((it / s.NS) - 1) & 1);
+                if (s.prof && blockIdx.x == 0 && it < 60) s.prof[it * 4] = clock64();
                 mbar_arrive_expect_tx(full + sa, s.R * row_bytes * mt);
-                for (int i = 0; i < mt; ++i)
-                    tma_load_3d(a_ring + sa * stage_bytes + i * s.a_tile_stride, &map_x, full + sa, 0, (t0 + i) * 128 - s.pad, b);
+                for (int i = 0; i < mt; ++i) {
+                    const int b = (u0 + i) / s.tiles, t = (u0 + i) - b * s.tiles;
+                    tma_load_3d(a_ring + sa * stage_bytes + i * s.a_tile_stride, &map_x, full + sa, 0, t * 128 - s.pad, b);
+                }
             }
         }
     } else if (warp <= 2) {
@@ -126,20 +144,32 @@ conv1d_fwd_narrow_kernel(const __grid_constant__ CUtensorMap map_x, const __grid
             const uint32_t sbo = 8 * row_bytes;
             mbar_wait(w_full, 0);
             for (int it = 0; it < my_items; ++it) {
-                const int item = blockIdx.x + it * gridDim.x;
-                const int t0 = (item % s.groups) * s.MT;
-                const int mt = s.tiles - t0 < s.MT ? s.tiles - t0 : s.MT;
+                int u0, mt;
+                narrow_item(s, blockIdx.x + it * gridDim.x, u0, mt);
                 const int sa = it % s.NS, buf = it & 1;
                 mbar_wait(full + sa, (it / s.NS) & 1);
+                if (s.prof && blockIdx.x == 0 && it < 60 && m == 0) s.prof[it * 4 + 1] = clock64();
                 if (it >= 2) mbar_wait(acc_empty + buf, ((it >> 1) - 1) & 1);
+                if (s.prof && blockIdx.x == 0 && it < 60 && m == 0) s.prof[it * 4 + 2] = clock64();
                 tc_fence_after_sync();
                 const uint32_t a_base = smem_u32(a_ring + sa * stage_bytes), w_base = smem_u32(w_smem);
-                for (int i = m; i < mt; i += 2) {
-                    const uint32_t d = tmem_base + buf * buf_cols + i * s.Cout;
-                    for (int k = 0; k < s.K; ++k)
-                        for (int j = 0; j < s.Cin / 16; ++j)     // 16 channels = 32 bytes inside the row
-                            mma_f16(d, smem_desc_krow(a_base + i * s.a_tile_stride + k * row_bytes + j * 32, sbo, layout),
-                                    smem_desc_krow(w_base + k * s.w_tap_bytes + j * 32, sbo, layout), idesc, (k | j) ? 1u : 0u);
+                // this warp's tiles are independent accumulators: interleave them so that the tensor pipe always has a second
+                // chain to work on while one MMA's accumulate is still in flight
+                const bool has0 = m < mt, has1 = m + 2 < mt;
+                const uint32_t d0 = tmem_base + buf * buf_cols + m * s.Cout, d1 = d0 + 2 * s.Cout;
+                const uint64_t a0 = smem_desc_krow(a_base + m * s.a_tile_stride, sbo, layout);
+                const uint64_t a1 = smem_desc_krow(a_base + (m + 2) * s.a_tile_stride, sbo, layout);
+                const uint64_t b0 = smem_desc_krow(w_base, sbo, layout);
+                const int nj = s.Cin / 16;                   // 16 channels = 32 bytes inside the row
+#pragma unroll 2
+                for (int k = 0; k < s.K; ++k) {
+                    const uint32_t ak = (uint32_t)(k * row_bytes) >> 4, bk = (uint32_t)(k * s.w_tap_bytes) >> 4;
+#pragma unroll 4
+                    for (int j = 0; j < nj; ++j) {
+                        const uint32_t acc = (k | j) ? 1u : 0u;
+                        if (has0) mma_f16(d0, a0 + (uint64_t)(ak + 2 * j), b0 + (uint64_t)(bk + 2 * j), idesc, acc);
+                        if (has1) mma_f16(d1, a1 + (uint64_t)(ak + 2 * j), b0 + (uint64_t)(bk + 2 * j), idesc, acc);
+                    }
                 }
                 mma_commit(empty + sa);                     // (a warp without a tile in this item still signals: counts are fixed)
                 mma_commit(acc_full + buf);
@@ -150,10 +180,10 @@ conv1d_fwd_narrow_kernel(const __grid_constant__ CUtensorMap map_x, const __grid
         const int e = (warp - 3) >> 2, q = warp & 3;
         const int r = q * 32 + lane;
         for (int it = e; it < my_items; it += 2) {
-            const int item = blockIdx.x + it * gridDim.x;
-            const int b = item / s.groups, t0 = (item % s.groups) * s.MT;
-            const int mt = s.tiles - t0 < s.MT ? s.tiles - t0 : s.MT;
+            int u0, mt;
+            narrow_item(s, blockIdx.x + it * gridDim.x, u0, mt);
             mbar_wait(acc_full + e, (it >> 1) & 1);
+            if (s.prof && blockIdx.x == 0 && it < 60 && q == 0 && lane == 0) s.prof[it * 4 + 3] = clock64();
             tc_fence_after_sync();
             // up to 64 accumulator columns go to registers at once; the TMEM buffer is handed back to the MMA warps as soon as the
             // last group has been loaded, BEFORE the conversion and the stores
@@ -173,7 +203,7 @@ conv1d_fwd_narrow_kernel(const __grid_constant__ CUtensorMap map_x, const __grid
                 for (int u = 0; u < 4; ++u) {
                     if (u < nch) {
                         const int col = cb + u * 16, i = col / s.Cout, c0 = col - i * s.Cout;
-                        const int l = (t0 + i) * 128 + r;
+                        const int b = (u0 + i) / s.tiles, l = ((u0 + i) - b * s.tiles) * 128 + r;
                         if (i < mt && l < s.Lout) {
                             uint32_t pk[8];
 #pragma unroll
@@ -197,26 +227,32 @@ conv1d_fwd_narrow_kernel(const __grid_constant__ CUtensorMap map_x, const __grid
     if (warp == 1) tmem_dealloc(tmem_base, tmem_cols);
 }
 
-int conv1d_fwd_narrow(const void* x, const void* w, const float* bias, void* y, int B, int L, int Cin, int Cout, int K, int pad,
-                      int relu, int Lout, cudaStream_t st) {
+static int fwd_narrow_impl(const void* x, const void* w, const float* bias, void* y, int B, int L, int Cin, int Cout, int K, int pad,
+                           int relu, int Lout, cudaStream_t st, bool packed) {
     if (env_int("CS_CONV_NARROW", 1) == 0) return -1;
-    if ((Cin != 16 && Cin != 32) || Cout > 64 || Cout % 16) return -1;   // rows of one swizzle span (Cin = 64: conv1d_sw128.cu)
+    // rows of one swizzle span; plain 64-channel layers belong to conv1d_sw128.cu, packed narrow layers come here as 64 x 64
+    if (!((Cin == 16 || Cin == 32) || (packed && Cin == 64)) || Cout > 64 || Cout % 16) return -1;
     if (Lout + K - 1 <= 64) return -1;                      // short windows: the sample-packing mode of the first generation
     NarrowFwd s;
     memset(&s, 0, sizeof(s));
+    s.prof = g_tiny_prof;
     s.B = B; s.L = L; s.Lout = Lout; s.Cin = Cin; s.Cout = Cout; s.K = K; s.pad = pad; s.relu = relu;
     s.R = 128 + K - 1;
     s.w_tap_bytes = (Cout * Cin * 2 + 1023) & ~1023;
     s.w_bytes = K * s.w_tap_bytes;
     if (s.w_bytes > 72 * 1024) return -1;                   // the whole weight tensor stays resident
     s.tiles = (Lout + 127) / 128;
-    s.MT = s.tiles >= 4 ? 4 : s.tiles;
-    while (2 * s.MT * Cout > 512) s.MT >>= 1;
-    s.groups = (s.tiles + s.MT - 1) / s.MT;
-    s.items = B * s.groups;
-    s.a_tile_stride = (s.R * Cin * 2 + 1023) & ~1023;
-    const size_t stage = (size_t)s.a_tile_stride * s.MT;
+    s.units = B * s.tiles;
     const size_t budget = 200 * 1024 - 1024 - s.w_bytes;
+    const int row_bytes = Cin * 2;
+    auto stage_of = [&](int mt) -> size_t { return (size_t)((s.R * row_bytes + 1023) & ~1023) * mt; };
+    s.MT = s.units >= 4 ? 4 : s.units;
+    // two tiles per MMA warp (two accumulate chains in flight) matter more than ring depth for the many-tap shapes
+    while (s.MT > 1 && (2 * s.MT * Cout > 512 || budget / stage_of(s.MT) < 3)) s.MT >>= 1;
+    s.a_tile_stride = (s.R * row_bytes + 1023) & ~1023;
+    s.items = (s.units + s.MT - 1) / s.MT;
+    const size_t stage = stage_of(s.MT);
+    s.stage_bytes = (int)stage;
     s.NS = (int)(budget / stage);
     if (s.NS > kNarrowMaxStages) s.NS = kNarrowMaxStages;
     if (s.NS < 3) return -1;
@@ -238,6 +274,11 @@ int conv1d_fwd_narrow(const void* x, const void* w, const float* bias, void* y, 
     conv1d_fwd_narrow_kernel<<<grid, kNarrowThreads, smem, st>>>(mx, mw, bias, (__nv_bfloat16*)y, s);
     CS_CUDA_OK(cudaGetLastError());
     return CS_OK;
+}
+
+int conv1d_fwd_narrow(const void* x, const void* w, const float* bias, void* y, int B, int L, int Cin, int Cout, int K, int pad,
+                      int relu, int Lout, cudaStream_t st) {
+    return fwd_narrow_impl(x, w, bias, y, B, L, Cin, Cout, K, pad, relu, Lout, st, false);
 }
 
 // ------------------------------------------------------------------------------------------------------------------
@@ -451,7 +492,7 @@ static uint8_t* pack_scratch() {
 }
 
 // Measured (B200, L = 500): packing wins where the tap count, not the row count, sets the time - C = 16 from K = 5
-// (K = 31, B = 4096: 73 us vs 183 us), C = 32 from K = 16; at K = 3 the row kernel is ahead (42 vs 50 us), and below ~64 K
+// (K = 31, B = 4096: 56 us vs 119 us), C = 32 from K = 16; at K = 3 the row kernel is ahead (37 vs 44 us), and below ~64 K
 // positions the extra weight-packing launch costs more than it saves.
 static bool packed_worth_it(int B, int L, int Cin, int K) {
     if (env_int("CS_CONV_PACK_MIN", -1) == 0) return true;                       // tests force the path
@@ -470,6 +511,10 @@ int conv1d_fwd_packed(const void* x, const void* w, const float* bias, void* y, 
     const int total = g.Kp * Cop * Cip;
     pack_weight_kernel<<<(total + 255) / 256, 256, 0, st>>>((const __nv_bfloat16*)w, bias, (__nv_bfloat16*)buf, bp, K, Cout, Cin, g.f, pad, g.dm_min, g.Kp);
     CS_CUDA_OK(cudaGetLastError());
+    if (env_int("CS_CONV_PACK_PERSISTENT", 1)) {             // the persistent pipelined kernel on 128-byte rows
+        const int rc = fwd_narrow_impl(x, buf, bp, y, B, L / g.f, Cip, Cop, g.Kp, g.padp, relu, Lout / g.f, st, true);
+        if (rc >= 0) return rc;
+    }
     return conv1d_fwd_sw128(x, buf, bp, y, B, L / g.f, Cip, Cop, g.Kp, g.padp, relu, Lout / g.f, st);
 }
 
