@@ -111,6 +111,7 @@ __global__ void __launch_bounds__(kCommThreads) fedavg_oneshot_kernel(const Comm
 // thread before the first use: ~5 MB in flight per GPU, enough to cover HBM and NVLink latency.
 // ------------------------------------------------------------------------------------------------
 constexpr int kU = 4;
+static int env_knob(const char* name, int dflt) { const char* e = getenv(name); return (e && *e) ? atoi(e) : dflt; }
 
 template <bool BF16> struct Wire4;
 template <> struct Wire4<false> {
@@ -269,6 +270,7 @@ struct InplaceCall {
     int channel;
 };
 
+template <int U2>
 __global__ void __launch_bounds__(kCommThreads) fedavg_inplace_kernel(const CommDev* ctxs, InplaceCall a) {
     const int er = blockIdx.y;
     const CommDev& c = ctxs[er];
@@ -284,7 +286,7 @@ __global__ void __launch_bounds__(kCommThreads) fedavg_inplace_kernel(const Comm
         const int s = c.rank;
         const long long g0 = s * gps + (long long)b * gpb;
         long long g1 = g0 + gpb; if (g1 > (s + 1) * gps) g1 = (s + 1) * gps; if (g1 > n4) g1 = n4;
-        constexpr int U2 = 2;
+        
         for (long long g = g0 + tid; g < g1; g += (long long)U2 * T) {
             float4 r[U2][kMaxRanks], q[U2];
 #pragma unroll
@@ -484,6 +486,7 @@ struct NvlsCall {
     int channel;
 };
 
+template <int kU>
 __global__ void __launch_bounds__(kCommThreads) fedavg_nvls_kernel(const CommDev* ctxs, NvlsCall a) {
     const CommDev& c = ctxs[0];
     const int P = c.world, b = blockIdx.x, nb = gridDim.x, T = blockDim.x, tid = threadIdx.x;
@@ -748,7 +751,11 @@ static int launch_inplace(const CommDev* ctxs, int ranks, const InplaceCall& a, 
     CS_REQUIRE(a.channel >= 0 && a.channel < kChannels, "aggregate_inplace: bad channel");
     int nb = pick_blocks(a.n, false);
     if (max_blocks > 0 && nb > max_blocks) nb = max_blocks;
-    const void* fn = (const void*)fedavg_inplace_kernel;
+    // independent 16-byte loads per thread and source rank before the first use (tuning knob, read at every call)
+    const int unroll = env_knob("CS_INPLACE_UNROLL", 2);
+    const void* fn = unroll == 1 ? (const void*)fedavg_inplace_kernel<1> : unroll == 3 ? (const void*)fedavg_inplace_kernel<3>
+                                                                                        : (const void*)fedavg_inplace_kernel<2>;
+    { const int cap = env_knob("CS_AGG_BLOCKS", 0); if (cap > 0 && nb > cap) nb = cap; }
     if (ranks > 1) {
         int per_sm = 1;
         CS_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, kCommThreads, 0));
@@ -841,7 +848,12 @@ int fedavg_aggregate_nvls(cs_comm* c, float* local, void* mc, float* prev, long 
     a.local = local; a.mc = (char*)mc; a.prev = prev; a.mom = mom; a.n = n; a.prescale = prescale; a.post_scale = post_scale;
     a.server_lr = server_lr; a.channel = channel;
     const CommDev* ctxs = c->dev;
-    fedavg_nvls_kernel<<<pick_blocks(n, false), kCommThreads, 0, st>>>(ctxs, a);
+    const int unroll = env_knob("CS_NVLS_UNROLL", 4);
+    int nb = pick_blocks(n, false);
+    { const int cap = env_knob("CS_AGG_BLOCKS", 0); if (cap > 0 && nb > cap) nb = cap; }
+    if (unroll == 8) fedavg_nvls_kernel<8><<<nb, kCommThreads, 0, st>>>(ctxs, a);
+    else if (unroll == 2) fedavg_nvls_kernel<2><<<nb, kCommThreads, 0, st>>>(ctxs, a);
+    else fedavg_nvls_kernel<4><<<nb, kCommThreads, 0, st>>>(ctxs, a);
     CS_CUDA_OK(cudaGetLastError());
     return CS_OK;
 }
