@@ -25,6 +25,8 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--n", type=int, default=24_150_000)
     ap.add_argument("--iters", type=int, default=20)
+    ap.add_argument("--blocks", default="0,96,64", help="CTA caps to try (0 = all SMs)")
+    ap.add_argument("--modes", default="on,nvls")
     a = ap.parse_args()
     rank, world, lr = launch.init_distributed()
     dev = setup_device(lr)
@@ -53,7 +55,8 @@ def main():
     out = {"world": world, "n": n, "mb": n * 4 / 1e6, "iters": a.iters,
            "p2p_floor_ms": 2.0 * wire / 770e9 * 1e3, "nvls_floor_ms": (wire + n * 4.0 / world) / 770e9 * 1e3, "rows": []}
     prev = torch.zeros(n, device=dev)
-    modes = ["on"] + (["nvls"] if world > 1 else [])
+    blocks = [int(b) for b in a.blocks.split(",")]
+    modes = [m for m in a.modes.split(",") if m == "on" or world > 1]
     for mode in modes:
         try:
             agg = FedAvgAggregator(n, dev, inplace=mode, channel=0)
@@ -62,8 +65,8 @@ def main():
             continue
         flat = agg.param_view
         flat.normal_()
-        knobs = ([("CS_INPLACE_UNROLL", u, "CS_AGG_BLOCKS", b) for u in (2, 1, 3) for b in (0, 96, 64)] if mode == "on"
-                 else [("CS_NVLS_UNROLL", u, "CS_AGG_BLOCKS", b) for u in (4, 2, 8) for b in (0, 96, 64)])
+        knobs = ([("CS_INPLACE_UNROLL", u, "CS_AGG_BLOCKS", b) for u in (2, 1, 3) for b in blocks] if mode == "on"
+                 else [("CS_NVLS_UNROLL", u, "CS_AGG_BLOCKS", b) for u in (4, 2, 8) for b in blocks])
         for k1, v1, k2, v2 in knobs:
             os.environ[k1], os.environ[k2] = str(v1), str(v2)
             ms = timed(lambda: agg.aggregate(flat, prev, 1.0 / world))
