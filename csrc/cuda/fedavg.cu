@@ -849,8 +849,10 @@ int fedavg_aggregate_nvls(cs_comm* c, float* local, void* mc, float* prev, long 
     a.server_lr = server_lr; a.channel = channel;
     const CommDev* ctxs = c->dev;
     const int unroll = env_knob("CS_NVLS_UNROLL", 4);
+    // The switch, not the SMs, sets the pace of multimem traffic: 8 x B200, 96.6 MB: 0.265 ms with 148 CTAs, 0.240 with 64,
+    // 0.232 with 32, 0.229 with 16 (profiles/r2/agg_sweep_n8*.json); powers of two partition the slices evenly.
     int nb = pick_blocks(n, false);
-    { const int cap = env_knob("CS_AGG_BLOCKS", 0); if (cap > 0 && nb > cap) nb = cap; }
+    { const int cap = env_knob("CS_AGG_BLOCKS", 32); if (cap > 0 && nb > cap) nb = cap; }
     if (unroll == 8) fedavg_nvls_kernel<8><<<nb, kCommThreads, 0, st>>>(ctxs, a);
     else if (unroll == 2) fedavg_nvls_kernel<2><<<nb, kCommThreads, 0, st>>>(ctxs, a);
     else fedavg_nvls_kernel<4><<<nb, kCommThreads, 0, st>>>(ctxs, a);
