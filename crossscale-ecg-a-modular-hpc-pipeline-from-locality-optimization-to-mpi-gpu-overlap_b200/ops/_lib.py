@@ -70,6 +70,17 @@ _CUDA_SIGS = {
     "cs_comm_create": (i32, [i32, i32, sz, C.POINTER(vp), vp, vp]),
     "cs_comm_connect": (i32, [vp, vp, vp]),
     "cs_comm_create_local": (i32, [i32, sz, C.POINTER(vp)]),
+    "cs_comm_create_external": (i32, [i32, i32, sz, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]),
+    "cs_comm_signal_bytes": (sz, []),
+    "cs_vmm_support": (i32, []),
+    "cs_vmm_alloc": (i32, [sz, i32, i32, C.POINTER(vp), C.POINTER(sz), C.POINTER(C.c_ulonglong), C.POINTER(i32)]),
+    "cs_vmm_import": (i32, [i32, sz, C.POINTER(vp), C.POINTER(C.c_ulonglong)]),
+    "cs_vmm_free": (i32, [vp, sz, C.c_ulonglong]),
+    "cs_vmm_mc_create": (i32, [i32, sz, C.POINTER(C.c_ulonglong), C.POINTER(i32)]),
+    "cs_vmm_mc_import": (i32, [i32, C.POINTER(C.c_ulonglong)]),
+    "cs_vmm_mc_add_device": (i32, [C.c_ulonglong]),
+    "cs_vmm_mc_bind_map": (i32, [C.c_ulonglong, C.c_ulonglong, sz, C.POINTER(vp)]),
+    "cs_vmm_close_fd": (i32, [i32]),
     "cs_comm_arena": (vp, [vp]),
     "cs_comm_peer_arena": (vp, [vp, i32]),
     "cs_comm_arena_bytes": (sz, [vp]),

@@ -14,6 +14,7 @@ checkpoint loads.
 """
 from __future__ import annotations
 
+import os
 from typing import Optional, Sequence
 
 import torch
@@ -66,20 +67,32 @@ class FedAvgAggregator:
         self.nvls = None
         self.param_view: Optional[torch.Tensor] = None
         self._weights = None
+        self._mc_ptr = 0
         if self.inplace and inplace == "nvls":
-            # parameters live in a torch symmetric-memory buffer that is also mapped at an NVSwitch multicast
-            # address; torch is used for that allocation / rendezvous only, the collective is our kernel
-            import torch.distributed._symmetric_memory as symm_mem
             if _world() < 2:
                 raise ValueError("NVLS aggregation needs at least 2 ranks")
-            t = symm_mem.empty(self.numel, dtype=torch.float32, device=self.device)
-            h = symm_mem.rendezvous(t, dist.group.WORLD)
-            if not int(h.multicast_ptr):
-                raise RuntimeError("this system offers no NVLS multicast mapping")
-            self.nvls = (t, h)
-            self.param_view = t
+            from . import vmm
+            if self.comm is None and (vmm.support() & 2) and os.environ.get("CROSSSCALE_NVLS_ALLOC", "vmm") == "vmm":
+                # the repo's own allocator: the arena is a VMM allocation bound to a multicast object (parallel/vmm.py)
+                self.comm = SymmetricComm(self.numel * 4, backend="vmm", multicast=True)
+                self._mc_ptr = int(self.comm.multicast_ptr)
+                if not self._mc_ptr:
+                    raise RuntimeError("this system offers no NVLS multicast mapping")
+                self.param_view = self.comm.arena_tensor(self.numel)
+                self.nvls = ("vmm", None)
+            else:
+                # fallback: a torch symmetric-memory buffer that is also mapped at a multicast address; torch is used for
+                # that allocation / rendezvous only, the collective is our kernel
+                import torch.distributed._symmetric_memory as symm_mem
+                t = symm_mem.empty(self.numel, dtype=torch.float32, device=self.device)
+                h = symm_mem.rendezvous(t, dist.group.WORLD)
+                if not int(h.multicast_ptr):
+                    raise RuntimeError("this system offers no NVLS multicast mapping")
+                self.nvls = (t, h)
+                self._mc_ptr = int(h.multicast_ptr)
+                self.param_view = t
         if backend == "kernel":
-            need = (4096 if self.nvls is not None else self.numel * 4 if self.inplace
+            need = (4096 if (self.nvls is not None and self.nvls[0] != "vmm") else self.numel * 4 if self.inplace
                     else int(_lib.cuda_lib().cs_fedavg_arena_bytes(self.numel, self.wire_bf16, _world())))
             if self.comm is None:
                 self.comm = SymmetricComm(need)
@@ -111,7 +124,7 @@ class FedAvgAggregator:
             use_prev = self.server_lr != 1.0
             if self.nvls is not None:
                 _lib.check(_lib.cuda_lib().cs_fedavg_aggregate_nvls(
-                    self.comm.handle, flat.data_ptr(), int(self.nvls[1].multicast_ptr), prev.data_ptr() if use_prev else None,
+                    self.comm.handle, flat.data_ptr(), self._mc_ptr, prev.data_ptr() if use_prev else None,
                     n, self._prescale, 1.0 / _world(), self.server_lr, _lib.ptr(mom) if self.reset_momentum else None,
                     self.channel, _lib.stream_ptr()), "cs_fedavg_aggregate_nvls")
                 self.launches += 1

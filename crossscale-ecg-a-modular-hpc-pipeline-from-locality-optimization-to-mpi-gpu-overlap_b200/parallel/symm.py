@@ -1,4 +1,5 @@
-"""Symmetric peer memory: one arena + signal pad per rank, mapped into every peer (CUDA IPC).
+"""Symmetric peer memory: one arena + signal pad per rank, mapped into every peer (CUDA IPC, or the repo's own
+VMM allocator with ``backend="vmm"``, which can also map the arena at an NVSwitch multicast address).
 
 This is the bootstrap layer under the in-kernel collectives: the only host-side
 communication is the one-time exchange of two 64-byte IPC handles per rank through the
@@ -20,22 +21,42 @@ HANDLE_BYTES = 64
 class SymmetricComm:
     """A communicator over peer-mapped arenas (real multi-process, one GPU per rank)."""
 
-    def __init__(self, arena_bytes: int, group: Optional[dist.ProcessGroup] = None):
+    def __init__(self, arena_bytes: int, group: Optional[dist.ProcessGroup] = None, backend: Optional[str] = None,
+                 multicast: bool = False):
+        """``backend``: "ipc" (cudaMalloc + CUDA IPC handles, the default) or "vmm" (the repo's own allocator,
+        ``parallel/vmm.py``: fd-exported VMM allocations; ``multicast=True`` additionally maps the arena at an NVSwitch
+        multicast address, ``self.multicast_ptr``).  Environment default: ``CROSSSCALE_SYMM``."""
+        import os
         lib = _lib.cuda_lib()
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
         self._h = C.c_void_p()
-        ah = (C.c_char * HANDLE_BYTES)()
-        sh = (C.c_char * HANDLE_BYTES)()
-        _lib.check(lib.cs_comm_create(self.rank, self.world, int(arena_bytes), C.byref(self._h), ah, sh),
-                   "cs_comm_create")
-        if self.world > 1:
-            gathered: List = [None] * self.world
-            dist.all_gather_object(gathered, (bytes(ah.raw), bytes(sh.raw)), group=group)
-            ahs = b"".join(g[0] for g in gathered)
-            shs = b"".join(g[1] for g in gathered)
-            _lib.check(lib.cs_comm_connect(self._h, ahs, shs), "cs_comm_connect")
-            dist.barrier(group=group)  # every rank has mapped every peer before first use
+        self.backend = backend or os.environ.get("CROSSSCALE_SYMM", "ipc")
+        self.multicast_ptr = 0
+        self._vmm = None
+        if self.backend == "vmm":
+            from .vmm import VmmBuffer
+            arena = (int(arena_bytes) + 4095) // 4096 * 4096
+            sig = int(lib.cs_comm_signal_bytes())
+            self._vmm = VmmBuffer(arena + sig, multicast=multicast, group=group)
+            ap = (C.c_void_p * self.world)(*[p for p in self._vmm.peer_ptrs])
+            sp = (C.c_void_p * self.world)(*[p + arena for p in self._vmm.peer_ptrs])
+            _lib.check(lib.cs_comm_create_external(self.rank, self.world, arena, ap, sp, C.byref(self._h)), "cs_comm_create_external")
+            self.multicast_ptr = self._vmm.multicast_ptr
+            if self.world > 1:
+                dist.barrier(group=group)
+        else:
+            ah = (C.c_char * HANDLE_BYTES)()
+            sh = (C.c_char * HANDLE_BYTES)()
+            _lib.check(lib.cs_comm_create(self.rank, self.world, int(arena_bytes), C.byref(self._h), ah, sh),
+                       "cs_comm_create")
+            if self.world > 1:
+                gathered: List = [None] * self.world
+                dist.all_gather_object(gathered, (bytes(ah.raw), bytes(sh.raw)), group=group)
+                ahs = b"".join(g[0] for g in gathered)
+                shs = b"".join(g[1] for g in gathered)
+                _lib.check(lib.cs_comm_connect(self._h, ahs, shs), "cs_comm_connect")
+                dist.barrier(group=group)  # every rank has mapped every peer before first use
         self.arena_bytes = int(lib.cs_comm_arena_bytes(self._h))
         self.emulated = False
 
@@ -65,6 +86,9 @@ class SymmetricComm:
             torch.cuda.synchronize()
             _lib.cuda_lib().cs_comm_destroy(self._h)
             self._h = C.c_void_p()
+            if self._vmm is not None:
+                self._vmm.close()
+                self._vmm = None
 
     def __del__(self):  # pragma: no cover
         try:

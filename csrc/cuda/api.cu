@@ -58,6 +58,8 @@ int ncl_to_nlc(const float*, void*, int, int, int, cudaStream_t);
 int nlc_to_ncl(const void*, float*, int, int, int, cudaStream_t);
 
 int comm_create(int, int, size_t, cs_comm**, void*, void*);
+int comm_create_external(int, int, size_t, void* const*, void* const*, cs_comm**);
+size_t comm_signal_bytes();
 int comm_connect(cs_comm*, const void*, const void*);
 int comm_create_local(int, size_t, cs_comm**);
 int comm_destroy(cs_comm*);
@@ -262,6 +264,10 @@ int cs_comm_create(int rank, int world, size_t bytes, cs_comm_t** out, void* ah,
     return comm_create(rank, world, bytes, (cs_comm**)out, ah, sh);
 }
 int cs_comm_connect(cs_comm_t* c, const void* ahs, const void* shs) { return comm_connect((cs_comm*)c, ahs, shs); }
+int cs_comm_create_external(int rank, int world, size_t bytes, void* const* arena, void* const* signals, cs_comm_t** out) {
+    return comm_create_external(rank, world, bytes, arena, signals, (cs_comm**)out);
+}
+size_t cs_comm_signal_bytes(void) { return comm_signal_bytes(); }
 int cs_comm_create_local(int world, size_t bytes, cs_comm_t** out) { return comm_create_local(world, bytes, (cs_comm**)out); }
 void* cs_comm_arena(cs_comm_t* c) { return comm_arena((cs_comm*)c, -1); }
 void* cs_comm_peer_arena(cs_comm_t* c, int r) { return comm_arena((cs_comm*)c, r); }

@@ -39,6 +39,7 @@ struct cs_comm {
     void* peer_arena[cs::kMaxRanks] = {};
     uint32_t* peer_signals[cs::kMaxRanks] = {};
     bool opened[cs::kMaxRanks] = {};
+    bool external = false;            // arena / signal mappings are owned by the caller (VMM allocator): never freed here
     cs::CommDev* dev = nullptr;       // device copy of the context
     cs_comm** group = nullptr;        // emulation: all members (owned by member 0)
     cs::CommDev* group_dev = nullptr; // emulation: contiguous array of `world` contexts

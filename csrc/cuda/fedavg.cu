@@ -628,6 +628,31 @@ int comm_connect(cs_comm* c, const void* ahs, const void* shs) {
     return upload_ctx(c, c->dev);
 }
 
+// Communicator over mappings the caller made itself (symm_vmm.cu: VMM allocations imported from the peers).  arena[r] /
+// signals[r]: this process's mapping of rank r's arena and signal pad (r == rank: the local allocation); the signal pad must
+// hold kSignalWords zeroed 32-bit words.
+int comm_create_external(int rank, int world, size_t bytes, void* const* arena, void* const* signals, cs_comm** out) {
+    CS_REQUIRE(world >= 1 && world <= kMaxRanks && rank >= 0 && rank < world, "comm: bad rank/world %d/%d", rank, world);
+    for (int r = 0; r < world; ++r) CS_REQUIRE(arena[r] && signals[r], "comm_create_external: null mapping for rank %d", r);
+    cs_comm* c = new cs_comm();
+    c->rank = rank; c->world = world; c->bytes = bytes; c->external = true;
+    CS_CUDA_OK(cudaGetDevice(&c->device));
+    c->arena = arena[rank]; c->signals = (uint32_t*)signals[rank];
+    CS_CUDA_OK(cudaMalloc((void**)&c->epochs, kChannels * kMaxBlocks * sizeof(uint32_t)));
+    CS_CUDA_OK(cudaMemset(c->epochs, 0, kChannels * kMaxBlocks * sizeof(uint32_t)));
+    CS_CUDA_OK(cudaHostAlloc((void**)&c->status_host, sizeof(int), cudaHostAllocMapped));
+    *c->status_host = 0;
+    CS_CUDA_OK(cudaHostGetDevicePointer((void**)&c->status, c->status_host, 0));
+    if (const char* e = getenv("CS_COMM_TIMEOUT_MS")) { const long long ms = atoll(e); if (ms > 0) c->timeout_ns = (unsigned long long)ms * 1000000ull; }
+    CS_CUDA_OK(cudaMalloc((void**)&c->dev, sizeof(CommDev)));
+    for (int r = 0; r < world; ++r) { c->peer_arena[r] = arena[r]; c->peer_signals[r] = (uint32_t*)signals[r]; }
+    int rc = upload_ctx(c, c->dev);
+    if (rc) return rc;
+    *out = c;
+    return CS_OK;
+}
+size_t comm_signal_bytes() { return kSignalWords * sizeof(uint32_t); }
+
 int comm_create_local(int world, size_t bytes, cs_comm** out) {
     CS_REQUIRE(world >= 1 && world <= kMaxRanks, "comm: bad world %d", world);
     cs_comm** g = new cs_comm*[world];
@@ -663,6 +688,11 @@ int comm_destroy(cs_comm* c) {
             delete g[r];
         }
         delete[] g;
+        return CS_OK;
+    }
+    if (c->external) {
+        cudaFree(c->epochs); cudaFreeHost(c->status_host); cudaFree(c->dev);
+        delete c;
         return CS_OK;
     }
     for (int r = 0; r < c->world; ++r)

@@ -292,6 +292,24 @@ int cs_comm_create(int rank, int world, size_t bytes, cs_comm_t** out, void* are
 /* Map every peer's arena and signal pad.  `arena_handles`/`signal_handles`: host arrays of
  * world * CS_IPC_HANDLE_BYTES gathered from all ranks (any host-side transport). */
 int cs_comm_connect(cs_comm_t* c, const void* arena_handles, const void* signal_handles);
+/* Communicator over mappings the caller made itself (the VMM allocator below): arena[r] / signals[r] = this process's
+ * mapping of rank r's arena (`bytes`) and zeroed signal pad (cs_comm_signal_bytes()); nothing is freed by cs_comm_destroy. */
+int cs_comm_create_external(int rank, int world, size_t bytes, void* const* arena, void* const* signals, cs_comm_t** out);
+size_t cs_comm_signal_bytes(void);
+
+/* Own symmetric-memory allocator (csrc/cuda/symm_vmm.cu): CUDA VMM allocations exported as POSIX file descriptors (sent to
+ * the peers over AF_UNIX sockets by crossscale/parallel/vmm.py), imported + mapped by every rank, optionally bound to an
+ * NVSwitch multicast object (NVLS).  cs_vmm_support(): bit 0 = fd-exportable VMM allocations, bit 1 = multicast. */
+int cs_vmm_support(void);
+int cs_vmm_alloc(size_t bytes, int for_multicast, int world, void** ptr, size_t* alloc_bytes, unsigned long long* handle, int* fd);
+int cs_vmm_import(int fd, size_t alloc_bytes, void** ptr, unsigned long long* handle);
+int cs_vmm_free(void* ptr, size_t alloc_bytes, unsigned long long handle);
+int cs_vmm_mc_create(int world, size_t alloc_bytes, unsigned long long* mc_handle, int* fd);
+int cs_vmm_mc_import(int fd, unsigned long long* mc_handle);
+int cs_vmm_mc_add_device(unsigned long long mc_handle);
+int cs_vmm_mc_bind_map(unsigned long long mc_handle, unsigned long long mem_handle, size_t alloc_bytes, void** mc_ptr);
+int cs_vmm_close_fd(int fd);
+
 /* Single-process emulation for tests/1-GPU: all `world` arenas live on the current device. */
 int cs_comm_create_local(int world, size_t bytes, cs_comm_t** out /* array of `world` */);
 void* cs_comm_arena(cs_comm_t* c);          /* this rank's arena (device pointer)              */

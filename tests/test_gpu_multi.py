@@ -60,11 +60,13 @@ def _run(world, script, tmp_path, port):
     return subprocess.run(cmd, cwd=REPO, env=env, capture_output=True, text=True, timeout=600)
 
 
-@pytest.mark.parametrize("world", [2, 4, 8])
-def test_fedavg_kernel_across_processes(world, tmp_path):
+@pytest.mark.parametrize("world,symm", [(2, "ipc"), (4, "ipc"), (8, "ipc"), (2, "vmm"), (8, "vmm")])
+def test_fedavg_kernel_across_processes(world, symm, tmp_path, monkeypatch):
+    """symm = vmm: the arenas are the repo's own fd-exported VMM allocations (parallel/vmm.py) instead of CUDA IPC handles"""
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs")
-    r = _run(world, WORKER, tmp_path, 29700 + world)
+    monkeypatch.setenv("CROSSSCALE_SYMM", symm)
+    r = _run(world, WORKER, tmp_path, 29700 + world + (10 if symm == "vmm" else 0))
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     line = [l for l in r.stdout.splitlines() if l.startswith("RESULT ")][-1]
     res = json.loads(line[7:])
@@ -174,24 +176,28 @@ for equal in (True, False):
     same = [torch.empty_like(agg.param_view) for _ in range(world)]
     dist.all_gather(same, agg.param_view.clone())
     res["equal" if equal else "weighted"] = {"err": err, "identical": all(torch.equal(same[0], s) for s in same),
-                                             "status": agg.comm.status()}
+                                             "status": agg.comm.status(),
+                                             "alloc": "vmm" if isinstance(agg.nvls[0], str) else "torch"}
 if rank == 0:
     print("RESULT " + json.dumps(res))
 launch.shutdown()
 '''
 
 
-@pytest.mark.parametrize("world", [2, 8])
-def test_fedavg_nvls_multimem_two_gpus(tmp_path, world):
+@pytest.mark.parametrize("world,alloc", [(2, "vmm"), (8, "vmm"), (2, "torch")])
+def test_fedavg_nvls_multimem_two_gpus(tmp_path, world, alloc, monkeypatch):
+    """alloc = vmm: the multicast mapping comes from the repo's own allocator (cuMulticastCreate / BindMem through
+    parallel/vmm.py); torch: the torch symmetric-memory fallback"""
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs")
-    r = _run(world, NVLS_WORKER, tmp_path, 29751 + world)
+    monkeypatch.setenv("CROSSSCALE_NVLS_ALLOC", alloc)
+    r = _run(world, NVLS_WORKER, tmp_path, 29751 + world + (30 if alloc == "torch" else 0))
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     res = json.loads([l for l in r.stdout.splitlines() if l.startswith("RESULT ")][-1][7:])
     if "skipped" in res:
         pytest.skip("no NVLS multicast here: " + res["skipped"])
     for key, v in res.items():
-        assert v["err"] < 2e-6 and v["identical"] and v["status"] == 0, (key, v)
+        assert v["err"] < 2e-6 and v["identical"] and v["status"] == 0 and v["alloc"] == alloc, (key, v)
 
 
 ROUND_WORKER = r'''
