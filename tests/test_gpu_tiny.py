@@ -95,8 +95,11 @@ def test_tcgen05_forward_backward_vs_fp32_oracle(amp_name, C, B, L):
         report.append((name, round(e, 4), round(e_amp, 4)))
         off += n
     print("rel-err (ours, torch-autocast) vs fp32:", report)
+    # bf16: the fused kernel keeps conv1, the head and every accumulation in fp32, so it must not lose more than cuDNN autocast
+    # does (measured: 0.5-0.8x of autocast's error on every tensor); fp16: both are at the 1e-3 level, where the order of the
+    # fp32 reductions decides - within 2x of autocast, or below 5e-3 outright
     for name, e, e_amp in report:
-        assert e < max(3e-2, 2.5 * e_amp), report
+        assert e < max(5e-3, (1.1 if amp_name == "bf16" else 2.0) * e_amp), report
 
 
 def test_autograd_bridge_matches_reference():
